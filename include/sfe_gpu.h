@@ -1,0 +1,162 @@
+/*
+ * sfe_gpu.h -- C ABI of libsfegpu.so, the B200 (sm_100a) implementation of simpleFE's libdsp
+ * sample-stream hot path: blkconv -> decimate -> resample, fed through ring_buffer.
+ *
+ * Plain pointers and sizes only; no C++/torch types.  Every entry point names the reference
+ * interface it stands behind (paths relative to the reference tree, wnmusic/simpleFE).
+ * There is NO CPU fallback anywhere in this library: without a usable CUDA device every
+ * create/process call fails (NULL / negative status) and sfe_last_error() says why.
+ *
+ * Two groups:
+ *  (1) single-object entry points -- exactly what the reference's C++ classes need, bound by the
+ *      drop-in headers include/libdsp/{blkconv,decimate,resample,ringbuf}.h and by the ctypes
+ *      `pydsp` module (simplefe_b200/pydsp.py, mirrors libdsp/test/pydsp.i).
+ *  (2) batched, additive entry points (sfe_chain_*) -- S independent IQ streams that share one
+ *      filter set; this is where the throughput is.  Per stream the result equals a fresh set of
+ *      reference objects per real component (I and Q) fed the same samples.
+ */
+#ifndef SFE_GPU_H_
+#define SFE_GPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library itself is built with -fvisibility=hidden */
+#endif
+
+#define SFE_OK 0
+#define SFE_ERR_ARG (-1)      /* bad argument (message in sfe_last_error) */
+#define SFE_ERR_CUDA (-2)     /* CUDA runtime/driver failure: fatal, never papered over */
+#define SFE_ERR_NODEV (-3)    /* no CUDA device / not sm_100 */
+#define SFE_ERR_CAP (-4)      /* caller-provided capacity too small */
+
+/* ---- library ---------------------------------------------------------------------------- */
+const char *sfe_version(void);
+const char *sfe_last_error(void);          /* thread-local, "" when none */
+int sfe_device_count(void);                /* >= 0, or negative status */
+int sfe_set_device(int device);            /* device used by objects created afterwards */
+int64_t sfe_kernel_launches(void);         /* kernels launched by this library since load */
+
+/* ---- raw memory / stream helpers (for hosts without their own CUDA bindings) -------------- */
+void *sfe_pinned_alloc(size_t bytes);      /* cudaHostAlloc; NULL on failure */
+void sfe_pinned_free(void *p);
+void *sfe_dev_alloc(size_t bytes);
+void sfe_dev_free(void *p);
+int sfe_memcpy_h2d(void *dst_dev, const void *src_host, size_t bytes, void *stream);
+int sfe_memcpy_d2h(void *dst_host, const void *src_dev, size_t bytes, void *stream);
+int sfe_stream_sync(void *stream);         /* NULL = the library's default stream */
+
+/* ---- (1a) blkconv: libdsp/blkconv.h:35-48, blkconv.cxx:34-122 ------------------------------ */
+typedef struct sfe_blkconv sfe_blkconv;
+/* blkconv::blkconv(float *taps, int n_taps, int fft_len)  blkconv.h:38.  Taps are copied.
+   fft_len must be a power of two in [32, 8192] and n_taps <= fft_len (else NULL + error). */
+sfe_blkconv *sfe_blkconv_create(const float *taps, int n_taps, int fft_len);
+int sfe_blkconv_blksize(sfe_blkconv *h);   /* blkconv::get_blksize  blkconv.h:40 = fft_len+1-n_taps */
+float *sfe_blkconv_buf(sfe_blkconv *h);    /* blkconv::get_process_buf blkconv.h:44: pinned host
+                                              buffer of fft_len+2 floats owned by the object */
+int sfe_blkconv_process(sfe_blkconv *h);   /* blkconv::process blkconv.h:48: consumes buf[0..blk),
+                                              leaves the next blk output samples there; returns
+                                              after the result is visible in host memory */
+void sfe_blkconv_destroy(sfe_blkconv *h);  /* blkconv::~blkconv */
+
+/* ---- (1b) decimate / resample: libdsp/decimate.h:33-46, resample.h:33-47 -------------------- */
+typedef struct sfe_polyphase sfe_polyphase;
+/* decimate::decimate(float *taps, int n_taps, int upsample, int blksize)  decimate.h:37 */
+sfe_polyphase *sfe_decimate_create(const float *taps, int n_taps, int upsample, int blksize);
+/* resample::resample(float *taps, int n_taps, int upsample, int blksize)  resample.h:39 */
+sfe_polyphase *sfe_resample_create(const float *taps, int n_taps, int upsample, int blksize);
+/* int process(float* in, int n_in, float *out, int out_len, float rate)  decimate.h:45 /
+   resample.h:47.  Returns the number of output samples.  On the reference's argument errors
+   (decimate.cxx:75-87, resample.cxx:91-98) prints the reference's message to stdout and
+   returns 0.  A CUDA failure returns a negative status. */
+int sfe_polyphase_process(sfe_polyphase *h, const float *in, int n_in, float *out, int out_len,
+                          float rate);
+void sfe_polyphase_destroy(sfe_polyphase *h);
+/* 1 = reproduce the reference's single-precision operation order bit for bit (separate multiply
+   and add, ascending taps); 0 (default) = fused multiply-add.  Applies to later process calls. */
+int sfe_polyphase_set_exact(sfe_polyphase *h, int exact);
+
+/* ---- (2) batched chain ---------------------------------------------------------------------- */
+enum {
+    SFE_IN_I16 = 0,   /* int16 I,Q interleaved; f = (float)s * (1.0f/32767.0f)        */
+    SFE_IN_U8 = 1,    /* device wire format, offset binary; f = (b-128)*(1.0f/127.0f)
+                         gr-simplefe/lib/source_c_impl.cc:121-132                                  */
+    SFE_IN_F32 = 2    /* float32 I,Q interleaved (complex64)                                       */
+};
+enum { SFE_KLASS_NONE = 0, SFE_KLASS_DECIMATE = 1, SFE_KLASS_RESAMPLE = 2 };
+enum {
+    SFE_FLAG_EXACT = 1,        /* polyphase stages in reference operation order (slow path)        */
+    SFE_FLAG_NO_FUSE = 2,      /* run blkconv and stage A as separate kernels even when fusable    */
+    SFE_FLAG_NO_TENSOR = 4     /* never use the tensor-core Toeplitz kernel                        */
+};
+
+typedef struct {
+    int klass;            /* SFE_KLASS_*; NONE = stage absent                                      */
+    const float *taps;    /* copied                                                                */
+    int n_taps;
+    int up;               /* `upsample` ctor argument                                              */
+    int blk;              /* `blksize` ctor argument = samples per reference process() call        */
+    float rate;           /* `rate` process() argument                                             */
+} sfe_stage_desc;
+
+typedef struct {
+    int in_fmt;           /* SFE_IN_*                                                              */
+    int n_streams;        /* S complex (IQ) streams, all sharing the filters below                 */
+    const float *bc_taps; /* blkconv stage (blkconv.h:38); bc_ntaps == 0 -> absent                 */
+    int bc_ntaps;
+    int bc_fft;
+    sfe_stage_desc a;     /* first polyphase stage (e.g. decimate)                                 */
+    sfe_stage_desc b;     /* second polyphase stage (e.g. resample)                                */
+    int flags;            /* SFE_FLAG_*                                                            */
+} sfe_chain_desc;
+
+typedef struct sfe_chain sfe_chain;
+
+sfe_chain *sfe_chain_create(const sfe_chain_desc *desc);
+void sfe_chain_destroy(sfe_chain *c);
+/* forget all stream state (overlap, histories, resampler phase): next call starts a new stream */
+int sfe_chain_reset(sfe_chain *c);
+/* upper bound of output samples per stream for a call with n_in input samples per stream */
+long sfe_chain_max_out(sfe_chain *c, long n_in);
+/* Streaming call, device buffers.  d_in: S rows of n_in complex samples in desc.in_fmt, row pitch
+   in_pitch (in complex samples).  d_out: S rows of complex64, row pitch out_pitch >= n_out.
+   *n_out receives the per-stream output count of this call (identical for all streams: the
+   output schedule is data independent).  Work is enqueued on `stream` (a cudaStream_t, NULL =
+   library default stream) and the call returns without synchronising.
+   Per stream the call is equivalent to feeding the reference objects: blkconv in blocks of
+   fft_len+1-n_taps, stage a in ceil(n_in/a.blk) process() calls of a.blk samples
+   (out_len = floor(a.blk/a.rate)+2), stage b likewise over stage a's output. */
+int sfe_chain_process_dev(sfe_chain *c, const void *d_in, long n_in, long in_pitch, void *d_out,
+                          long out_pitch, long *n_out, void *stream);
+/* Same, host buffers (pinned for full speed): the S streams are cut into groups whose H2D copy,
+   kernels and D2H copy are double-buffered on separate CUDA streams (the GPU-side successor of
+   ring_buffer's producer/consumer decoupling).  Returns after the result is in h_out. */
+int sfe_chain_process_host(sfe_chain *c, const void *h_in, long n_in, long in_pitch, void *h_out,
+                           long out_pitch, long *n_out);
+/* describe the kernels the last process call used, e.g. "toeplitz_i8+polyphase_generic" */
+const char *sfe_chain_plan(sfe_chain *c);
+/* Per-kernel timing for roofline reports: when enabled, sfe_chain_process_dev brackets the main
+   kernel of every op with CUDA events on the caller's stream (cost: two event records per op). */
+int sfe_chain_n_ops(sfe_chain *c);
+const char *sfe_chain_op_name(sfe_chain *c, int op);
+int sfe_chain_profile_enable(sfe_chain *c, int on);
+/* mean duration in ms of op's main kernel over the calls since enable / the previous read
+   (synchronises on the recorded events); *n_samples = launches averaged */
+int sfe_chain_profile_read(sfe_chain *c, int op, float *mean_ms, int *n_samples);
+
+/* ---- sample format helpers (device wire formats) ---------------------- */
+/* float -> 10-bit DAC words, 4 samples -> 5 bytes: examples/bpsk/bpsk.cxx:76-101,
+   gr-simplefe/lib/sink_c_impl.cc:118-144.  n must be a multiple of 4; device pointers. */
+int sfe_pack_dac10_dev(const float *d_in, long n, uint8_t *d_out, void *stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* SFE_GPU_H_ */

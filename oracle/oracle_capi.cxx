@@ -138,9 +138,12 @@ static int run_stage(const sfeo_stage &st, std::vector<float> &x, std::vector<fl
     return produced;
 }
 
-static int run_component(const sfeo_chain_cfg &c, const void *iq, long n, int comp, std::vector<float> &res)
+struct scratch { std::vector<float> x, y; };  /* per-thread, reused across streams (no mmap churn) */
+
+static int run_component(const sfeo_chain_cfg &c, const void *iq, long n, int comp, std::vector<float> &res, scratch &sc)
 {
-    std::vector<float> x((size_t)n), y;
+    std::vector<float> &x = sc.x, &y = sc.y;
+    x.resize((size_t)n);
     if (c.in_fmt == 0) {
         const int16_t *p = static_cast<const int16_t *>(iq);
         const float q = 1.0f / 32767.0f;
@@ -169,7 +172,7 @@ static int run_component(const sfeo_chain_cfg &c, const void *iq, long n, int co
     }
     if (c.a.klass) { run_stage(c.a, x, y); x.swap(y); }
     if (c.b.klass) { run_stage(c.b, x, y); x.swap(y); }
-    res.swap(x);
+    res.assign(x.begin(), x.end());
     return (int)res.size();
 }
 
@@ -185,10 +188,11 @@ int sfeo_chain_run(const sfeo_chain_cfg *cfg, const void *iq, int n_streams, lon
     std::vector<int> fail(n_threads, 0);
     auto work = [&](int tid) {
         std::vector<float> ri, rq;
+        scratch sc;
         for (int s = tid; s < n_streams; s += n_threads) {
             const char *src = static_cast<const char *>(iq) + in_stride * s;
-            const int ni = run_component(c, src, n, 0, ri);
-            const int nq = run_component(c, src, n, 1, rq);
+            const int ni = run_component(c, src, n, 0, ri, sc);
+            const int nq = run_component(c, src, n, 1, rq, sc);
             if (ni != nq || ni > out_cap) { fail[tid] = 1; n_out[s] = ni; continue; }
             float *o = out + (size_t)s * out_cap * 2;
             for (int i = 0; i < ni; i++) { o[2 * i] = ri[i]; o[2 * i + 1] = rq[i]; }

@@ -1,0 +1,97 @@
+"""Batched many-stream chain: [blkconv] -> [stage a] -> [stage b] on S IQ streams sharing one filter
+set (additive API over sfe_chain_* in include/sfe_gpu.h)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from ._lib import ChainDesc, SfeError, check, last_error, lib, _f32p
+
+IN_I16, IN_U8, IN_F32 = 0, 1, 2
+KLASS_NONE, KLASS_DECIMATE, KLASS_RESAMPLE = 0, 1, 2
+FLAG_EXACT, FLAG_NO_FUSE, FLAG_NO_TENSOR = 1, 2, 4
+_NP_DT = {IN_I16: np.int16, IN_U8: np.uint8, IN_F32: np.float32}
+BYTES_PER_SAMPLE = {IN_I16: 4, IN_U8: 2, IN_F32: 8}
+
+
+def stage(klass: int, taps, up: int, blk: int, rate: float) -> dict:
+    return dict(klass=klass, taps=taps, up=up, blk=blk, rate=rate)
+
+
+class Chain:
+    def __init__(self, n_streams: int, in_fmt: int = IN_I16, blkconv=None, stage_a=None, stage_b=None, flags: int = 0,
+                 device: int | None = None):
+        self._l = lib()
+        if device is not None:
+            check(self._l.sfe_set_device(int(device)), "sfe_set_device")
+        d = ChainDesc()
+        d.in_fmt, d.n_streams, d.flags = int(in_fmt), int(n_streams), int(flags)
+        keep = []
+        if blkconv is not None:
+            t = np.ascontiguousarray(np.asarray(blkconv[0], np.float32))
+            keep.append(t)
+            d.bc_taps, d.bc_ntaps, d.bc_fft = t.ctypes.data_as(_f32p), len(t), int(blkconv[1])
+        for name, st in (("a", stage_a), ("b", stage_b)):
+            if st is None:
+                continue
+            t = np.ascontiguousarray(np.asarray(st["taps"], np.float32))
+            keep.append(t)
+            s = getattr(d, name)
+            s.klass, s.taps, s.n_taps = int(st["klass"]), t.ctypes.data_as(_f32p), len(t)
+            s.up, s.blk, s.rate = int(st["up"]), int(st["blk"]), float(st["rate"])
+        self._h = self._l.sfe_chain_create(C.byref(d))
+        if not self._h:
+            raise SfeError(f"sfe_chain_create: {last_error()}")
+        self.n_streams, self.in_fmt = int(n_streams), int(in_fmt)
+
+    @property
+    def plan(self) -> str:
+        return self._l.sfe_chain_plan(self._h).decode()
+
+    def profile(self, on: bool = True):
+        check(self._l.sfe_chain_profile_enable(self._h, int(on)), "sfe_chain_profile_enable")
+
+    def profile_read(self):
+        """[(op name, mean kernel ms, launches)] since profiling was enabled / last read"""
+        out = []
+        for i in range(self._l.sfe_chain_n_ops(self._h)):
+            ms, n = C.c_float(0), C.c_int(0)
+            check(self._l.sfe_chain_profile_read(self._h, i, C.byref(ms), C.byref(n)), "sfe_chain_profile_read")
+            out.append((self._l.sfe_chain_op_name(self._h, i).decode(), float(ms.value), int(n.value)))
+        return out
+
+    def reset(self):
+        check(self._l.sfe_chain_reset(self._h), "sfe_chain_reset")
+
+    def max_out(self, n_in: int) -> int:
+        return int(self._l.sfe_chain_max_out(self._h, int(n_in)))
+
+    def process_dev(self, d_in: int, n_in: int, in_pitch: int, d_out: int, out_pitch: int, stream: int = 0) -> int:
+        """Raw device pointers (ints); enqueues on `stream` (cudaStream_t as int) and returns n_out."""
+        n_out = C.c_long(0)
+        check(self._l.sfe_chain_process_dev(self._h, d_in, int(n_in), int(in_pitch), d_out, int(out_pitch),
+                                            C.byref(n_out), stream), "sfe_chain_process_dev")
+        return int(n_out.value)
+
+    def process_host_raw(self, h_in: int, n_in: int, in_pitch: int, h_out: int, out_pitch: int) -> int:
+        n_out = C.c_long(0)
+        check(self._l.sfe_chain_process_host(self._h, h_in, int(n_in), int(in_pitch), h_out, int(out_pitch),
+                                             C.byref(n_out)), "sfe_chain_process_host")
+        return int(n_out.value)
+
+    def process(self, iq: np.ndarray) -> np.ndarray:
+        """iq: (S, N, 2) host array in the chain's input format -> complex64 (S, n_out)."""
+        iq = np.ascontiguousarray(iq, dtype=_NP_DT[self.in_fmt])
+        S, N, two = iq.shape
+        if S != self.n_streams or two != 2:
+            raise ValueError("iq must be (n_streams, N, 2)")
+        cap = self.max_out(N)
+        out = np.zeros((S, cap), np.complex64)
+        n = self.process_host_raw(iq.ctypes.data, N, N, out.ctypes.data, cap)
+        return out[:, :n]
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._l.sfe_chain_destroy(h)

@@ -1,0 +1,237 @@
+// blkconv_kernel.cu -- K1: FFT block convolver for batches of IQ streams (sm_100a).
+//
+// Replaces blkconv::process (libdsp/blkconv.cxx:77-110) plus the caller-side sample conversion.
+// The reference does overlap-ADD on one real stream with FFTW r2c/c2r.  Here one complex FFT
+// carries I and Q of a stream at once (real taps => (I*h) + j(Q*h)), and blocks use overlap-SAVE
+// so that every FFT block is independent: block b of a stream reads fft_len samples starting
+// n_taps-1 before its first output and discards the first n_taps-1 results.  The hop equals the
+// reference's block size fft_len+1-n_taps (blkconv.cxx:47).  Both formulations compute the same
+// causal linear convolution from zero state; they differ by float rounding only.
+//
+// One FFT = N/16 threads, 16 points per thread and pass:
+//   forward  : radix-16 DIF passes (last pass radix 2/4/8 when log2 N is not a multiple of 4),
+//              data exchanged through padded shared memory between passes
+//   multiply : by the tap spectrum, stored in the same digit-reversed order and pre-scaled by 1/N
+//              (blkconv.cxx:92-101), fused between the last forward and first inverse butterfly
+//   inverse  : the mirrored DIT passes with conjugated twiddles, then overlap discard + store.
+// No reordering pass is ever needed: forward leaves digit-reversed order, inverse consumes it.
+#include "sfe_fft.cuh"
+#include "kernels.h"
+
+namespace sfe {
+
+namespace {
+
+__host__ __device__ constexpr int ilog2(int n) { return n <= 1 ? 0 : 1 + ilog2(n >> 1); }
+
+template <int N> struct Plan {
+    static constexpr int LOGN = ilog2(N);
+    static constexpr int FULL = LOGN / 4;                  // radix-16 passes
+    static constexpr int LASTR = 1 << (LOGN % 4);          // 1 = none
+    static constexpr int NP = FULL + (LASTR > 1 ? 1 : 0);  // passes
+    static constexpr int TPF = N / 16;                     // threads per FFT
+    static constexpr int PADN = N + N / 16;                // padded shared-memory length
+    static __host__ __device__ constexpr int radix(int p) { return p < FULL ? 16 : LASTR; }
+    static __host__ __device__ constexpr int size(int p)   // sub-transform length entering pass p
+    {
+        int m = N;
+        for (int i = 0; i < p; i++) m /= radix(i);
+        return m;
+    }
+};
+
+__device__ __forceinline__ int phi(int a) { return a + (a >> 4); }  // bank-conflict padding
+
+struct Ctx {
+    const BlkconvParams &p;
+    int stream;     // stream row of this FFT
+    long blk0;      // first output sample of this block
+    bool active;
+};
+
+// source of pass 0 (forward): global memory, with format conversion, history and zero fill
+__device__ __forceinline__ float2 load_input(const Ctx &c, int i)
+{
+    if (!c.active) return make_float2(0.f, 0.f);
+    const long n = c.blk0 - c.p.ov + i;
+    if (c.p.in_real) {
+        if (n >= c.p.in.n) return make_float2(0.f, 0.f);
+        const float *cur = reinterpret_cast<const float *>(c.p.in.cur);
+        const float *hist = reinterpret_cast<const float *>(c.p.in.hist);
+        if (n >= 0) return make_float2(__ldg(cur + (long)c.stream * c.p.in.pitch + n), 0.f);
+        const long h = c.p.in.H + n;
+        return h < 0 ? make_float2(0.f, 0.f) : make_float2(__ldg(hist + (long)c.stream * c.p.in.H + h), 0.f);
+    }
+    return load_sample(c.p.in, c.stream, n);
+}
+
+__device__ __forceinline__ void store_output(const Ctx &c, int i, float2 v)
+{
+    if (!c.active || i < c.p.ov) return;                   // overlap discard
+    const long n = c.blk0 + (i - c.p.ov);
+    if (n >= c.p.in.n) return;
+    if (c.p.in_real)
+        reinterpret_cast<float *>(c.p.out)[(long)c.stream * c.p.out_pitch + n] = v.x;
+    else
+        reinterpret_cast<float2 *>(c.p.out)[(long)c.stream * c.p.out_pitch + n] = v;
+}
+
+// ---- one forward (DIF) pass -------------------------------------------------------------------
+// P = pass index. FIRST: read from global. The last pass leaves its result in registers (vout).
+template <int N, int P, bool KEEP>
+__device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 (&keep)[16])
+{
+    using PL = Plan<N>;
+    constexpr int R = PL::radix(P), M = PL::size(P), S = M / R, NB = 16 / R;
+#pragma unroll
+    for (int u = 0; u < NB; u++) {
+        const int beta = t + u * PL::TPF;
+        const int b = (beta / S) * M, j = beta % S;
+        float2 v[R];
+#pragma unroll
+        for (int k = 0; k < R; k++) v[k] = P == 0 ? load_input(c, b + j + k * S) : X[phi(b + j + k * S)];
+        dft_dif<R, -1>(v);
+#pragma unroll
+        for (int sl = 0; sl < R; sl++) {
+            constexpr int dummy = 0;
+            (void)dummy;
+            const int q = brev<R>(sl);
+            float2 y = v[sl];
+            if (S > 1 && q != 0) y = cmul(y, __ldg(c.p.tw + (N / M) * j * q));
+            if (KEEP) keep[u * R + q] = y;
+            else X[phi(b + j + q * S)] = y;
+        }
+    }
+}
+
+// ---- one inverse (DIT) pass: exact mirror of fwd_pass<P> ----------------------------------------
+template <int N, int P, bool FROMREG>
+__device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 (&keep)[16])
+{
+    using PL = Plan<N>;
+    constexpr int R = PL::radix(P), M = PL::size(P), S = M / R, NB = 16 / R;
+#pragma unroll
+    for (int u = 0; u < NB; u++) {
+        const int beta = t + u * PL::TPF;
+        const int b = (beta / S) * M, j = beta % S;
+        float2 v[R];
+#pragma unroll
+        for (int q = 0; q < R; q++) {
+            float2 y = FROMREG ? keep[u * R + q] : X[phi(b + j + q * S)];
+            if (S > 1 && q != 0) y = cmul_conj(y, __ldg(c.p.tw + (N / M) * j * q));
+            v[q] = y;
+        }
+        dft_dif<R, +1>(v);
+#pragma unroll
+        for (int sl = 0; sl < R; sl++) {
+            const int k = brev<R>(sl);
+            if (P == 0) store_output(c, b + j + k * S, v[sl]);
+            else X[phi(b + j + k * S)] = v[sl];
+        }
+    }
+}
+
+template <int N, int P> struct FwdChain {
+    static __device__ __forceinline__ void run(float2 *X, int t, const Ctx &c, float2 (&keep)[16])
+    {
+        constexpr bool last = (P == Plan<N>::NP - 1);
+        fwd_pass<N, P, last>(X, t, c, keep);
+        if constexpr (!last) {
+            __syncthreads();
+            FwdChain<N, P + 1>::run(X, t, c, keep);
+        }
+    }
+};
+
+template <int N, int P> struct InvChain {
+    static __device__ __forceinline__ void run(float2 *X, int t, const Ctx &c, float2 (&keep)[16])
+    {
+        constexpr bool first = (P == Plan<N>::NP - 1);
+        inv_pass<N, P, first>(X, t, c, keep);
+        if constexpr (P > 0) {
+            __syncthreads();
+            InvChain<N, P - 1>::run(X, t, c, keep);
+        }
+    }
+};
+
+template <int N, int FPB>
+__global__ void __launch_bounds__(Plan<N>::TPF *FPB) blkconv_fft_kernel(const BlkconvParams p)
+{
+    using PL = Plan<N>;
+    extern __shared__ float2 smem[];
+    const int f = threadIdx.x / PL::TPF, t = threadIdx.x % PL::TPF;
+    const long id = (long)blockIdx.x * FPB + f;
+    const long total = (long)p.n_streams * p.n_blocks;
+    Ctx c{p, 0, 0, id < total};
+    if (c.active) {
+        c.stream = (int)(id / p.n_blocks);
+        c.blk0 = (id % p.n_blocks) * (long)p.hop;
+    }
+    float2 *X = smem + f * PL::PADN;
+    float2 keep[16];
+
+    FwdChain<N, 0>::run(X, t, c, keep);
+
+    // thread-private spectrum slice: last pass has S = 1, element index = R*beta + q
+    constexpr int RL = PL::radix(PL::NP - 1), NB = 16 / RL;
+    if (p.mode == BLKCONV_MODE_SPECTRUM) {
+        // tap spectrum in the kernel's own digit-reversed order, pre-scaled (blkconv.cxx:50,60-69)
+        if (c.active) {
+#pragma unroll
+            for (int u = 0; u < NB; u++)
+#pragma unroll
+                for (int q = 0; q < RL; q++) {
+                    const float2 v = keep[u * RL + q];
+                    reinterpret_cast<float2 *>(p.out)[(t + u * PL::TPF) * RL + q] = make_float2(v.x * p.scale, v.y * p.scale);
+                }
+        }
+        return;
+    }
+#pragma unroll
+    for (int u = 0; u < NB; u++)
+#pragma unroll
+        for (int q = 0; q < RL; q++)
+            keep[u * RL + q] = cmul(keep[u * RL + q], __ldg(p.hp + (t + u * PL::TPF) * RL + q));
+
+    InvChain<N, PL::NP - 1>::run(X, t, c, keep);
+}
+
+template <int N> int launch_n(const BlkconvParams &p, cudaStream_t st)
+{
+    using PL = Plan<N>;
+    constexpr int FPB = PL::TPF >= 128 ? 1 : 128 / PL::TPF;
+    const long total = (long)p.n_streams * p.n_blocks;
+    if (total <= 0) return SFE_OK;
+    const size_t smem = sizeof(float2) * PL::PADN * FPB;
+    auto kern = blkconv_fft_kernel<N, FPB>;
+    if (smem > 48 * 1024 &&
+        !SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)))
+        return SFE_ERR_CUDA;
+    const long grid = (total + FPB - 1) / FPB;
+    kern<<<(unsigned)grid, PL::TPF * FPB, smem, st>>>(p);
+    count_launch();
+    return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+}
+
+}  // namespace
+
+int launch_blkconv(int fft_len, const BlkconvParams &p, cudaStream_t st)
+{
+    switch (fft_len) {
+        case 32: return launch_n<32>(p, st);
+        case 64: return launch_n<64>(p, st);
+        case 128: return launch_n<128>(p, st);
+        case 256: return launch_n<256>(p, st);
+        case 512: return launch_n<512>(p, st);
+        case 1024: return launch_n<1024>(p, st);
+        case 2048: return launch_n<2048>(p, st);
+        case 4096: return launch_n<4096>(p, st);
+        case 8192: return launch_n<8192>(p, st);
+        default:
+            set_error("blkconv: fft_len must be a power of two in [32, 8192]");
+            return SFE_ERR_ARG;
+    }
+}
+
+}  // namespace sfe

@@ -1,0 +1,527 @@
+// chain.cu -- batched chain object (sfe_chain_*): S independent IQ streams through
+// [blkconv] -> [polyphase stage a] -> [polyphase stage b], all streams sharing one filter set.
+//
+// Kernel plan chosen at create time:
+//   * a polyphase stage whose float32 step rate*L is an integer multiple of L produces a uniform,
+//     phase-0 schedule for ever (mu == 0, exact in float32 while blk*L < 2^24): it runs on the
+//     decimating-FIR kernel (K2d);
+//   * blkconv followed by such a stage is FUSED: the two FIRs are convolved into one tap set (in
+//     double) and only the retained outputs are ever computed -- the FFT convolver's full-rate
+//     intermediate never exists;
+//   * everything else runs stage by stage: K1 (FFT blkconv) and K2g (generic polyphase with the
+//     host-generated float32 schedule).
+// Stream state (input history per stage, resampler phase) is carried across calls so a stream may
+// be fed in arbitrary pieces.
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+namespace sfe {
+const float2 *chain_twiddles(int dev, int N);
+float2 *chain_spectrum(int dev, const float *taps, int n_taps, int N, cudaStream_t st);
+bool chain_device_ready(int *dev);
+}  // namespace sfe
+
+using namespace sfe;
+
+namespace {
+
+enum OpKind { OP_BLKCONV, OP_DECIM, OP_POLY };
+
+struct Op {
+    OpKind kind;
+    int in_fmt;                    // format of this op's input rows
+    int H = 0;                     // history samples kept of the input
+    void *hist[2] = {nullptr, nullptr};
+    // blkconv
+    int N = 0, bc_ntaps = 0, hop = 0, ov = 0;
+    const float2 *tw = nullptr;
+    float2 *hp = nullptr;
+    // polyphase
+    int up = 1, blk = 0, T = 0;
+    float rate = 1.f;
+    float *d_taps = nullptr;
+    WalkState ws;
+    Schedule sched;
+    SchedEntry *d_sched = nullptr;
+    size_t d_sched_cap = 0;
+    // decimating FIR
+    int D = 0, QLP = 0;
+    float *d_gp = nullptr;
+    // per call
+    long n_in = 0, n_out = 0;
+    std::string name;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;  // profiling: (start, stop) per launch
+};
+
+struct Workspace {
+    std::vector<void *> mid;       // intermediate row buffers between ops (complex64)
+    std::vector<size_t> mid_bytes;
+    void *d_in = nullptr, *d_out = nullptr;  // staging for process_host
+    size_t in_bytes = 0, out_bytes = 0;
+    cudaStream_t st = nullptr;
+};
+
+}  // namespace
+
+struct sfe_chain {
+    int dev = 0, S = 0, in_fmt = 0, flags = 0;
+    std::vector<Op> ops;
+    int cur = 0;                   // which history buffer holds the live state
+    Workspace ws[2];
+    std::string plan;
+    bool profile = false;
+};
+
+namespace {
+
+bool integral_step(const sfe_stage_desc &s, long *step)
+{
+    const float f = s.rate * (float)s.up;
+    if (!(f >= 1.0f) || f != floorf(f)) return false;
+    if ((double)s.blk * s.up + f >= 16777216.0) return false;  // float32 time stays exact
+    *step = (long)f;
+    return true;
+}
+
+std::vector<float> padded_taps(const sfe_stage_desc &s)
+{
+    // decimate.cxx:42-51 pads an even count with one zero tap; zero padding never changes results
+    const int T = (s.klass == SFE_KLASS_DECIMATE && s.n_taps % 2 == 0) ? s.n_taps + 1 : s.n_taps;
+    std::vector<float> t((size_t)T, 0.f);
+    memcpy(t.data(), s.taps, sizeof(float) * s.n_taps);
+    return t;
+}
+
+bool upload(float **d, const std::vector<float> &h)
+{
+    return SFE_CUDA(cudaMalloc(d, sizeof(float) * h.size())) &&
+           SFE_CUDA(cudaMemcpy(*d, h.data(), sizeof(float) * h.size(), cudaMemcpyHostToDevice));
+}
+
+bool make_decim(Op &op, const std::vector<double> &g, int D)
+{
+    op.kind = OP_DECIM;
+    op.D = D;
+    op.T = (int)g.size();
+    int QL = (op.T + D - 1) / D;
+    op.QLP = (QL + 7) / 8 * 8;
+    std::vector<float> gp((size_t)D * op.QLP, 0.f);
+    for (int j = 0; j < op.T; j++) gp[(size_t)(j % D) * op.QLP + j / D] = (float)g[j];
+    op.H = op.T + D;
+    return upload(&op.d_gp, gp);
+}
+
+bool alloc_hist(Op &op, int S)
+{
+    const size_t bytes = (size_t)S * op.H * fmt_bytes(op.in_fmt);
+    for (int i = 0; i < 2; i++)
+        if (!SFE_CUDA(cudaMalloc(&op.hist[i], bytes ? bytes : 1)) || !SFE_CUDA(cudaMemset(op.hist[i], 0, bytes))) return false;
+    return true;
+}
+
+long stage_max_out(const Op &op, long n)
+{
+    if (op.kind == OP_BLKCONV) return n;
+    const double r = op.kind == OP_DECIM ? (double)op.D : (double)op.rate;
+    const long calls = op.blk > 0 ? (n + op.blk - 1) / op.blk : 1;
+    return (long)((double)n / r) + 2 * calls + 4;
+}
+
+bool ensure(void **p, size_t *have, size_t need)
+{
+    if (*have >= need) return true;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *have = 0;
+    if (!SFE_CUDA(cudaMalloc(p, need))) return false;
+    *have = need;
+    return true;
+}
+
+// host part of a call: advance every op's schedule for n_in new samples per stream
+void plan_call(sfe_chain *c, long n_in)
+{
+    long n = n_in;
+    for (Op &op : c->ops) {
+        op.n_in = n;
+        if (op.kind == OP_BLKCONV) {
+            op.n_out = n;
+        } else {
+            walk_batch(op.ws, op.up, op.blk, op.rate, n, op.sched);
+            op.n_out = (long)op.sched.e.size();
+        }
+        n = op.n_out;
+    }
+}
+
+// device part: run all ops for stream rows [s0, s0+ns) on workspace w
+int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long in_pitch, void *d_out, long out_pitch,
+            cudaStream_t st)
+{
+    const void *src = d_in;
+    long src_pitch = in_pitch;
+    const size_t nops = c->ops.size();
+    if (w.mid.size() < nops) {
+        w.mid.resize(nops, nullptr);
+        w.mid_bytes.resize(nops, 0);
+    }
+    for (size_t i = 0; i < nops; i++) {
+        Op &op = c->ops[i];
+        const bool last = i + 1 == nops;
+        void *dst = d_out;
+        long dst_pitch = out_pitch;
+        if (!last) {
+            dst_pitch = op.n_out > 0 ? op.n_out : 1;
+            if (!ensure(&w.mid[i], &w.mid_bytes[i], sizeof(float2) * (size_t)ns * dst_pitch)) return SFE_ERR_CUDA;
+            dst = w.mid[i];
+        }
+        const int eb = fmt_bytes(op.in_fmt);
+        const char *hist_old = static_cast<const char *>(op.hist[c->cur]) + (size_t)s0 * op.H * eb;
+        char *hist_new = static_cast<char *>(op.hist[c->cur ^ 1]) + (size_t)s0 * op.H * eb;
+        StreamView in{src, hist_old, src_pitch, op.H, op.n_in, op.in_fmt};
+        int rc = SFE_OK;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (c->profile && op.ev.size() < 256) {
+            if (!SFE_CUDA(cudaEventCreate(&e0)) || !SFE_CUDA(cudaEventCreate(&e1)) || !SFE_CUDA(cudaEventRecord(e0, st)))
+                return SFE_ERR_CUDA;
+        }
+        if (op.kind == OP_BLKCONV) {
+            BlkconvParams p{};
+            p.in = in;
+            p.in_real = 0;
+            p.out = dst;
+            p.out_pitch = dst_pitch;
+            p.n_streams = ns;
+            p.n_blocks = (op.n_in + op.hop - 1) / op.hop;
+            p.hop = op.hop;
+            p.ov = op.ov;
+            p.tw = op.tw;
+            p.hp = op.hp;
+            p.mode = BLKCONV_MODE_CONV;
+            rc = launch_blkconv(op.N, p, st);
+        } else if (op.kind == OP_DECIM && op.n_out > 0) {
+            DecimParams p{};
+            p.in = in;
+            p.out = static_cast<float2 *>(dst);
+            p.out_pitch = dst_pitch;
+            p.n_streams = ns;
+            p.n_out = op.n_out;
+            p.gp = op.d_gp;
+            p.D = op.D;
+            p.QLP = op.QLP;
+            // uniform phase-0 schedule: positions are multiples of `up` (or -1 when up == 1)
+            p.n_first = op.sched.pos0 >= 0 ? op.sched.pos0 / op.up : -1;
+            rc = launch_decim_fir(p, st);
+        } else if (op.kind == OP_POLY && op.n_out > 0) {
+            PolyParams p{};
+            p.in = in;
+            p.in_real = 0;
+            p.out = dst;
+            p.out_pitch = dst_pitch;
+            p.n_streams = ns;
+            p.n_out = op.n_out;
+            p.taps = op.d_taps;
+            p.n_taps = op.T;
+            p.up = op.up;
+            p.uniform = op.sched.uniform ? 1 : 0;
+            p.pos0 = op.sched.pos0;
+            p.step = op.sched.step;
+            p.sched = op.d_sched;
+            p.exact = (c->flags & SFE_FLAG_EXACT) ? 1 : 0;
+            rc = launch_poly_generic(p, st);
+        }
+        if (rc != SFE_OK) return rc;
+        if (e0) {
+            if (!SFE_CUDA(cudaEventRecord(e1, st))) return SFE_ERR_CUDA;
+            op.ev.emplace_back(e0, e1);
+        }
+        rc = launch_save_tail(hist_new, hist_old, src, src_pitch, op.n_in, op.H, eb, ns, st);
+        if (rc != SFE_OK) return rc;
+        src = dst;
+        src_pitch = dst_pitch;
+    }
+    return SFE_OK;
+}
+
+// schedules that are not closed-form must be on the device before the kernels run
+int upload_schedules(sfe_chain *c, cudaStream_t st)
+{
+    for (Op &op : c->ops) {
+        if (op.kind != OP_POLY || op.sched.uniform || op.n_out == 0) continue;
+        const size_t need = sizeof(SchedEntry) * (size_t)op.n_out;
+        if (op.d_sched_cap < need) {
+            if (op.d_sched) cudaFree(op.d_sched);
+            op.d_sched = nullptr;
+            op.d_sched_cap = 0;
+            if (!SFE_CUDA(cudaMalloc(&op.d_sched, need * 2))) return SFE_ERR_CUDA;
+            op.d_sched_cap = need * 2;
+        }
+        // pageable source: the runtime stages the copy before returning, so the vector may be reused
+        if (!SFE_CUDA(cudaMemcpyAsync(op.d_sched, op.sched.e.data(), need, cudaMemcpyHostToDevice, st))) return SFE_ERR_CUDA;
+    }
+    return SFE_OK;
+}
+
+}  // namespace
+
+extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
+{
+    if (!d || d->n_streams < 1 || d->in_fmt < SFE_IN_I16 || d->in_fmt > SFE_IN_F32) {
+        set_error("chain: bad descriptor (n_streams >= 1, in_fmt in {I16,U8,F32})");
+        return nullptr;
+    }
+    const bool has_bc = d->bc_ntaps > 0, has_a = d->a.klass != SFE_KLASS_NONE, has_b = d->b.klass != SFE_KLASS_NONE;
+    if (!has_bc && !has_a && !has_b) {
+        set_error("chain: no stage present");
+        return nullptr;
+    }
+    if (has_b && !has_a) {
+        set_error("chain: stage b without stage a");
+        return nullptr;
+    }
+    if (has_bc && (!d->bc_taps || d->bc_ntaps > d->bc_fft || d->bc_fft < 32 || d->bc_fft > 8192 ||
+                   (d->bc_fft & (d->bc_fft - 1)))) {
+        set_error("chain: blkconv needs 1 <= n_taps <= fft_len, fft_len a power of two in [32, 8192]");
+        return nullptr;
+    }
+    for (const sfe_stage_desc *s : {&d->a, &d->b}) {
+        if (s->klass == SFE_KLASS_NONE) continue;
+        const bool rate_ok = s->klass == SFE_KLASS_DECIMATE ? s->rate >= 1.0f : s->rate >= 1.0f / (float)s->up;
+        if (!s->taps || s->n_taps < 1 || s->up < 1 || s->blk < 1 || !rate_ok) {
+            set_error("chain: bad polyphase stage (taps, upsample >= 1, blk >= 1, rate >= 1 for decimate, >= 1/upsample for resample)");
+            return nullptr;
+        }
+    }
+    int dev = 0;
+    if (!chain_device_ready(&dev)) return nullptr;
+
+    sfe_chain *c = new sfe_chain;
+    c->dev = dev;
+    c->S = d->n_streams;
+    c->in_fmt = d->in_fmt;
+    c->flags = d->flags;
+    bool ok = true;
+    int fmt = d->in_fmt;
+    long step_a = 0;
+    const bool a_decim = has_a && integral_step(d->a, &step_a) && step_a % d->a.up == 0 && !(d->flags & SFE_FLAG_EXACT);
+    const bool fuse = has_bc && a_decim && !(d->flags & SFE_FLAG_NO_FUSE);
+
+    if (has_bc && !fuse) {
+        Op op{};
+        op.kind = OP_BLKCONV;
+        op.in_fmt = fmt;
+        op.N = d->bc_fft;
+        op.bc_ntaps = d->bc_ntaps;
+        op.hop = d->bc_fft + 1 - d->bc_ntaps;  // blkconv.cxx:47
+        op.ov = d->bc_ntaps - 1;               // blkconv.cxx:48
+        op.H = op.ov;
+        op.tw = chain_twiddles(dev, op.N);
+        op.hp = chain_spectrum(dev, d->bc_taps, d->bc_ntaps, op.N, nullptr);
+        ok = ok && op.tw && op.hp;
+        op.name = "blkconv_fft" + std::to_string(op.N);
+        c->ops.push_back(op);
+        c->plan += op.name;
+        fmt = SFE_IN_F32;
+    }
+    for (int which = 0; which < 2 && ok; which++) {
+        const sfe_stage_desc &s = which == 0 ? d->a : d->b;
+        if (s.klass == SFE_KLASS_NONE) continue;
+        Op op{};
+        op.in_fmt = fmt;
+        op.up = s.up;
+        op.blk = s.blk;
+        op.rate = s.rate;
+        const std::vector<float> t = padded_taps(s);
+        long step = 0;
+        const bool decim = integral_step(s, &step) && step % s.up == 0 && !(d->flags & SFE_FLAG_EXACT);
+        if (!c->plan.empty()) c->plan += "+";
+        const size_t plan_mark = c->plan.size();
+        if (decim) {
+            // phase-0 taps g[q] = taps[q*up]; optionally convolved with the blkconv taps (fusion)
+            std::vector<double> g;
+            for (size_t q = 0; q * s.up < t.size(); q++) g.push_back((double)t[q * s.up]);
+            while (g.size() > 1 && g.back() == 0.0) g.pop_back();
+            if (which == 0 && fuse) {
+                std::vector<double> f(g.size() + d->bc_ntaps - 1, 0.0);
+                for (size_t i = 0; i < g.size(); i++)
+                    for (int j = 0; j < d->bc_ntaps; j++) f[i + j] += g[i] * (double)d->bc_taps[j];
+                g.swap(f);
+                c->plan += "fused(blkconv*decim_fir)";
+            } else {
+                c->plan += "decim_fir";
+            }
+            ok = ok && make_decim(op, g, (int)(step / s.up));
+            c->plan += "/D" + std::to_string(op.D) + "T" + std::to_string(op.T);
+        } else {
+            op.kind = OP_POLY;
+            op.T = (int)t.size();
+            op.H = (op.T - 1) / s.up + 1;
+            ok = ok && upload(&op.d_taps, t);
+            c->plan += "polyphase_generic/L" + std::to_string(s.up) + "T" + std::to_string(op.T);
+        }
+        op.name = c->plan.substr(plan_mark);
+        c->ops.push_back(op);
+        fmt = SFE_IN_F32;
+    }
+    for (Op &op : c->ops) ok = ok && alloc_hist(op, c->S);
+    for (int i = 0; i < 2 && ok; i++) ok = SFE_CUDA(cudaStreamCreateWithFlags(&c->ws[i].st, cudaStreamNonBlocking));
+    if (!ok) {
+        sfe_chain_destroy(c);
+        return nullptr;
+    }
+    return c;
+}
+
+extern "C" void sfe_chain_destroy(sfe_chain *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->dev);
+    cudaDeviceSynchronize();
+    for (Op &op : c->ops) {
+        cudaFree(op.hist[0]);
+        cudaFree(op.hist[1]);
+        cudaFree(op.hp);
+        cudaFree(op.d_taps);
+        cudaFree(op.d_gp);
+        cudaFree(op.d_sched);
+    }
+    for (Workspace &w : c->ws) {
+        for (void *m : w.mid) cudaFree(m);
+        cudaFree(w.d_in);
+        cudaFree(w.d_out);
+        if (w.st) cudaStreamDestroy(w.st);
+    }
+    delete c;
+}
+
+extern "C" int sfe_chain_reset(sfe_chain *c)
+{
+    if (!c) return SFE_ERR_ARG;
+    if (!SFE_CUDA(cudaSetDevice(c->dev)) || !SFE_CUDA(cudaDeviceSynchronize())) return SFE_ERR_CUDA;
+    for (Op &op : c->ops) {
+        op.ws = WalkState{};
+        const size_t bytes = (size_t)c->S * op.H * fmt_bytes(op.in_fmt);
+        for (int i = 0; i < 2; i++)
+            if (!SFE_CUDA(cudaMemset(op.hist[i], 0, bytes))) return SFE_ERR_CUDA;
+    }
+    return SFE_OK;
+}
+
+extern "C" long sfe_chain_max_out(sfe_chain *c, long n_in)
+{
+    if (!c) return SFE_ERR_ARG;
+    long n = n_in;
+    for (const Op &op : c->ops) n = stage_max_out(op, n);
+    return n;
+}
+
+extern "C" const char *sfe_chain_plan(sfe_chain *c) { return c ? c->plan.c_str() : ""; }
+extern "C" int sfe_chain_n_ops(sfe_chain *c) { return c ? (int)c->ops.size() : SFE_ERR_ARG; }
+extern "C" const char *sfe_chain_op_name(sfe_chain *c, int op)
+{
+    return (c && op >= 0 && op < (int)c->ops.size()) ? c->ops[op].name.c_str() : "";
+}
+extern "C" int sfe_chain_profile_enable(sfe_chain *c, int on)
+{
+    if (!c) return SFE_ERR_ARG;
+    c->profile = on != 0;
+    return SFE_OK;
+}
+extern "C" int sfe_chain_profile_read(sfe_chain *c, int op, float *mean_ms, int *n_samples)
+{
+    if (!c || op < 0 || op >= (int)c->ops.size() || !mean_ms || !n_samples) return SFE_ERR_ARG;
+    Op &o = c->ops[op];
+    double sum = 0;
+    int n = 0;
+    for (auto &pr : o.ev) {
+        float ms = 0;
+        if (!SFE_CUDA(cudaEventSynchronize(pr.second)) || !SFE_CUDA(cudaEventElapsedTime(&ms, pr.first, pr.second))) return SFE_ERR_CUDA;
+        sum += ms;
+        n++;
+        cudaEventDestroy(pr.first);
+        cudaEventDestroy(pr.second);
+    }
+    o.ev.clear();
+    *mean_ms = n ? (float)(sum / n) : 0.f;
+    *n_samples = n;
+    return SFE_OK;
+}
+
+extern "C" int sfe_chain_process_dev(sfe_chain *c, const void *d_in, long n_in, long in_pitch, void *d_out,
+                                     long out_pitch, long *n_out, void *stream)
+{
+    if (!c || !d_in || !d_out || n_in < 0 || in_pitch < n_in) {
+        set_error("chain_process_dev: bad arguments");
+        return SFE_ERR_ARG;
+    }
+    if (!SFE_CUDA(cudaSetDevice(c->dev))) return SFE_ERR_CUDA;
+    plan_call(c, n_in);
+    const long no = c->ops.back().n_out;
+    if (n_out) *n_out = no;
+    if (out_pitch < no) {
+        set_error("chain_process_dev: out_pitch smaller than the output count " + std::to_string(no));
+        return SFE_ERR_CAP;  // note: the schedule state has advanced; call sfe_chain_reset
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = upload_schedules(c, st);
+    if (rc != SFE_OK) return rc;
+    rc = run_ops(c, c->ws[0], 0, c->S, d_in, in_pitch, d_out, out_pitch, st);
+    if (rc != SFE_OK) return rc;
+    c->cur ^= 1;
+    return SFE_OK;
+}
+
+extern "C" int sfe_chain_process_host(sfe_chain *c, const void *h_in, long n_in, long in_pitch, void *h_out,
+                                      long out_pitch, long *n_out)
+{
+    if (!c || !h_in || !h_out || n_in < 0 || in_pitch < n_in) {
+        set_error("chain_process_host: bad arguments");
+        return SFE_ERR_ARG;
+    }
+    if (!SFE_CUDA(cudaSetDevice(c->dev))) return SFE_ERR_CUDA;
+    plan_call(c, n_in);
+    const long no = c->ops.back().n_out;
+    if (n_out) *n_out = no;
+    if (out_pitch < no) {
+        set_error("chain_process_host: out_pitch smaller than the output count " + std::to_string(no));
+        return SFE_ERR_CAP;
+    }
+    const int eb = fmt_bytes(c->in_fmt);
+    // stream groups of ~64 MiB input: H2D(g+1) overlaps kernels(g) overlaps D2H(g-1) on two CUDA streams
+    const size_t row_in = (size_t)n_in * eb;
+    int gs = (int)((64u << 20) / (row_in ? row_in : 1));
+    if (gs < 1) gs = 1;
+    if (gs > c->S) gs = c->S;
+    if (c->S >= 4 && gs > (c->S + 3) / 4) gs = (c->S + 3) / 4;  // at least 4 groups so that copies overlap
+    int rc = upload_schedules(c, c->ws[0].st);
+    if (rc != SFE_OK) return rc;
+    if (!SFE_CUDA(cudaStreamSynchronize(c->ws[0].st))) return SFE_ERR_CUDA;
+    const long opitch = no > 0 ? no : 1;
+    int g = 0;
+    for (int s0 = 0; s0 < c->S; s0 += gs, g++) {
+        Workspace &w = c->ws[g & 1];
+        const int ns = c->S - s0 < gs ? c->S - s0 : gs;
+        if (!ensure(&w.d_in, &w.in_bytes, (size_t)gs * row_in) ||
+            !ensure(&w.d_out, &w.out_bytes, sizeof(float2) * (size_t)gs * opitch))
+            return SFE_ERR_CUDA;
+        const char *src = static_cast<const char *>(h_in) + (size_t)s0 * in_pitch * eb;
+        if (!SFE_CUDA(cudaMemcpy2DAsync(w.d_in, row_in, src, (size_t)in_pitch * eb, row_in, ns, cudaMemcpyHostToDevice, w.st)))
+            return SFE_ERR_CUDA;
+        rc = run_ops(c, w, s0, ns, w.d_in, n_in, w.d_out, opitch, w.st);
+        if (rc != SFE_OK) return rc;
+        if (no > 0) {
+            char *dst = static_cast<char *>(h_out) + sizeof(float2) * (size_t)s0 * out_pitch;
+            if (!SFE_CUDA(cudaMemcpy2DAsync(dst, sizeof(float2) * out_pitch, w.d_out, sizeof(float2) * opitch,
+                                            sizeof(float2) * no, ns, cudaMemcpyDeviceToHost, w.st)))
+                return SFE_ERR_CUDA;
+        }
+    }
+    for (Workspace &w : c->ws)
+        if (!SFE_CUDA(cudaStreamSynchronize(w.st))) return SFE_ERR_CUDA;
+    c->cur ^= 1;
+    return SFE_OK;
+}

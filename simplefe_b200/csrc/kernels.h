@@ -1,0 +1,64 @@
+// kernels.h -- launch interfaces of the libsfegpu kernels (internal; the public ABI is include/sfe_gpu.h)
+#pragma once
+#include "schedule.h"
+#include "sfe_common.cuh"
+
+namespace sfe {
+
+// ---- K1: FFT block convolver (blkconv_kernel.cu) ------------------------------------------------
+enum { BLKCONV_MODE_CONV = 0, BLKCONV_MODE_SPECTRUM = 1 };
+struct BlkconvParams {
+    StreamView in;        // raw input (+history of ov samples)
+    int in_real;          // 1: input/output are float (one real stream per row), else complex
+    void *out;            // complex64 (or float) rows
+    long out_pitch;
+    int n_streams;
+    long n_blocks;        // FFT blocks per stream = ceil(n / hop)
+    int hop;              // fft_len + 1 - n_taps (blkconv.cxx:47)
+    int ov;               // n_taps - 1          (blkconv.cxx:48)
+    const float2 *tw;     // exp(-2 pi i k / N), k < N
+    const float2 *hp;     // tap spectrum, kernel (digit-reversed) order, pre-scaled by 1/N
+    int mode;
+    float scale;          // spectrum mode: 1/N (blkconv.cxx:50)
+};
+int launch_blkconv(int fft_len, const BlkconvParams &p, cudaStream_t st);
+
+// ---- K2g: generic polyphase stage, one thread per output (polyphase_kernel.cu) ------------------
+struct PolyParams {
+    StreamView in;
+    int in_real;          // 1: float real rows in / float out (single-object API)
+    void *out;
+    long out_pitch;
+    int n_streams;
+    long n_out;
+    const float *taps;    // device, n_taps floats (already padded like the reference ctor)
+    int n_taps;
+    int up;
+    int uniform;          // 1: pos = pos0 + k*step, mu = 0
+    long pos0, step;
+    const SchedEntry *sched;  // device, n_out entries when !uniform
+    int exact;            // reference operation order (separate multiply/add)
+};
+int launch_poly_generic(const PolyParams &p, cudaStream_t st);
+
+// ---- K2d: decimating FIR on CUDA cores, register tiled (polyphase_kernel.cu) --------------------
+// y[k] = sum_j g[j] * x[n_first + D*k - j]
+struct DecimParams {
+    StreamView in;
+    float2 *out;
+    long out_pitch;
+    int n_streams;
+    long n_out;
+    const float *gp;      // device: plane-major taps [D][QLP], gp[r][q] = g[D*q + r] (zero padded)
+    int D, QLP;
+    long n_first;
+};
+int launch_decim_fir(const DecimParams &p, cudaStream_t st);
+
+// ---- small utilities (util_kernels.cu) -----------------------------------------------------------
+// hist_new[s][0..H) <- last H samples of (hist_old ++ cur[0..n)) for every stream row; elem = bytes per sample
+int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long pitch, long n, int H, int elem, int n_streams,
+                     cudaStream_t st);
+int launch_pack_dac10(const float *in, long n, uint8_t *out, cudaStream_t st);
+
+}  // namespace sfe

@@ -1,0 +1,42 @@
+// schedule.h -- host-side output-time schedule of the polyphase stages.
+//
+// The reference walks a *float32* time variable over the L-times upsampled grid
+// (libdsp/decimate.cxx:73,96-127; libdsp/resample.cxx:89,119-150).  Which grid positions are
+// produced, the interpolation weight mu and the left-over rule depend only on (rate, upsample,
+// n_in, out_len) and on three scalars carried between calls -- never on the samples.  The GPU
+// kernels therefore take the schedule as input; this file generates it with the reference's
+// exact single-precision recurrence so that output counts and sample indices are bit-exact.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace sfe {
+
+struct WalkState {        // decimate.h:55-59 / resample.h:56-59
+    int pos = 0;          // m_pos: next output position on the upsampled grid, relative to the
+                          //        first sample of the next call
+    float mu = 0.0f;      // m_mu
+    bool held = false;    // m_is_leftover: an output straddles the call boundary
+};
+
+struct SchedEntry {
+    int32_t pos;          // grid position of the left interpolation point, relative to the first
+                          // sample of the *batch* (may be -1 for a held-over output)
+    float mu;             // out = s(pos)*(1-mu) + mu*s(pos+1)
+};
+
+struct Schedule {
+    std::vector<SchedEntry> e;  // one per output, in output order
+    bool uniform = false;       // all mu == 0 and pos = pos0 + k*step
+    int64_t pos0 = 0, step = 0;
+};
+
+// One reference process() call: appends the outputs of a call with n_in samples whose first
+// sample sits at batch offset `base_in`; updates st.  Returns the number of outputs appended.
+int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t base_in,
+              std::vector<SchedEntry> &out);
+
+// A batch of n_in samples fed as ceil(n_in/blk) calls of blk samples, out_len = floor(blk/rate)+2.
+void walk_batch(WalkState &st, int up, int blk, float rate, int64_t n_in, Schedule &s);
+
+}  // namespace sfe

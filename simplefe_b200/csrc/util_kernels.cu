@@ -1,0 +1,67 @@
+// util_kernels.cu -- state carry and wire-format helpers.
+#include "kernels.h"
+
+namespace sfe {
+
+namespace {
+
+// hist_new[s][i] = (hist_old[s] ++ cur[s][0..n))[n + i], i < H.  Works on 16-bit units so that
+// every sample format (2, 4, 8 bytes) shares one kernel.
+__global__ void save_tail_kernel(uint16_t *hn, const uint16_t *ho, const uint16_t *cur, long pitch_u, long n_u,
+                                 int H_u, int n_streams)
+{
+    const int s = blockIdx.y;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < H_u; i += (long)gridDim.x * blockDim.x) {
+        const long src = n_u + i - H_u;  // index into cur when >= 0, else into the old history
+        hn[(long)s * H_u + i] = src >= 0 ? cur[(long)s * pitch_u + src] : ho[(long)s * H_u + (H_u + src)];
+    }
+}
+
+// examples/bpsk/bpsk.cxx:76-101 / gr-simplefe/lib/sink_c_impl.cc:118-144:
+//   u = ((short)(x*511) + 512) & 0x3FF ; 4 words -> 5 bytes, the four 2-bit tops first
+__global__ void pack_dac10_kernel(const float *in, long n4, uint8_t *out)
+{
+    const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n4) return;
+    const float4 x = reinterpret_cast<const float4 *>(in)[g];
+    const float v[4] = {x.x, x.y, x.z, x.w};
+    unsigned u[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const short sh = (short)(int)__fmul_rn(v[k], 511.0f);  // C float->short: truncation toward zero
+        u[k] = ((unsigned)(sh + 512)) & 0x3FFu;
+    }
+    uint8_t *o = out + g * 5;
+    o[0] = (uint8_t)((u[0] >> 8) | ((u[1] >> 8) << 2) | ((u[2] >> 8) << 4) | ((u[3] >> 8) << 6));
+    o[1] = (uint8_t)(u[0] & 0xFF);
+    o[2] = (uint8_t)(u[1] & 0xFF);
+    o[3] = (uint8_t)(u[2] & 0xFF);
+    o[4] = (uint8_t)(u[3] & 0xFF);
+}
+
+}  // namespace
+
+int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long pitch, long n, int H, int elem,
+                     int n_streams, cudaStream_t st)
+{
+    if (H <= 0 || n_streams <= 0) return SFE_OK;
+    const int u = elem / 2;
+    const int H_u = H * u;
+    dim3 grid((unsigned)((H_u + 255) / 256), (unsigned)n_streams);
+    if (grid.x > 64) grid.x = 64;
+    save_tail_kernel<<<grid, 256, 0, st>>>(static_cast<uint16_t *>(hist_new), static_cast<const uint16_t *>(hist_old),
+                                           static_cast<const uint16_t *>(cur), pitch * u, n * u, H_u, n_streams);
+    count_launch();
+    return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+}
+
+int launch_pack_dac10(const float *in, long n, uint8_t *out, cudaStream_t st)
+{
+    if (n <= 0) return SFE_OK;
+    const long n4 = n / 4;
+    pack_dac10_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(in, n4, out);
+    count_launch();
+    return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+}
+
+}  // namespace sfe

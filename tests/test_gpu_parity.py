@@ -1,0 +1,236 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI (ctypes), against the CPU oracle
+on identical seeded inputs, against the committed golden fixtures, and through size-independent
+properties (chunk invariance, linearity).  Tolerances are north_star's: conversion and indexing
+bit-exact; float32 outputs nRMS <= 1e-5 and peak-normalised max error <= 1e-4."""
+import os
+
+import numpy as np
+import pytest
+
+import fixtures as F
+
+pytestmark = pytest.mark.gpu
+
+KNOWN = dict(np.load(os.path.join(F.GOLDEN, "known.npz")))
+CHAIN = dict(np.load(os.path.join(F.GOLDEN, "chain.npz")))
+
+
+def _sine():
+    return np.sin(0.02 * np.pi * np.arange(1024)).astype(np.float32)
+
+
+# ---- single-object drop-in API (pydsp call shapes) -------------------------------------------------
+
+def test_blkconv_known_answer(gpu_lib):
+    from simplefe_b200 import pydsp
+    bc = pydsp.blkconv([1, 1, 1, 1, 1], 32)          # libdsp/test/test_blkconv.cxx:6-34
+    assert bc.get_blksize() == 28
+    buf = bc.get_process_buf()
+    buf[:28] = 1.0
+    bc.process()
+    np.testing.assert_allclose(buf[:28], [1, 2, 3, 4] + [5] * 24, atol=1e-5)
+    buf[:28] = 0.0
+    bc.process()
+    np.testing.assert_allclose(buf[:28], [4, 3, 2, 1] + [0] * 24, atol=1e-5)
+
+
+@pytest.mark.parametrize("taps,fft", [("lp255", 4096), ("rrc111", 2048), ("rrc551", 8192), ("taps31", 64), ("taps31", 128),
+                                      ("taps31", 256), ("rrc111", 512), ("rrc111", 1024)])
+def test_blkconv_object_vs_oracle(gpu_lib, oracle_lib, taps, fft):
+    from oracle import oracle as O
+    from simplefe_b200 import pydsp
+    t = F.taps(taps)
+    rng = np.random.default_rng(11)
+    bc = pydsp.blkconv(t, fft)
+    blk = bc.get_blksize()
+    x = rng.normal(0, 0.25, 5 * blk + 17).astype(np.float32)
+    ref = O.Blkconv(t, fft, lib=oracle_lib).filter(x)
+    got = np.empty_like(x)
+    buf = bc.get_process_buf()
+    for off in range(0, len(x), blk):
+        m = min(blk, len(x) - off)
+        buf[:m] = x[off:off + m]
+        buf[m:blk] = 0.0
+        bc.process()
+        got[off:off + m] = buf[:m]
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
+
+
+@pytest.mark.parametrize("name,cls,rate", [("resample_077", "resample", 0.77), ("resample_177", "resample", 1.77),
+                                            ("decimate_177", "decimate", 1.77), ("decimate_8", "decimate", 8.0)])
+@pytest.mark.parametrize("exact", [False, True])
+def test_polyphase_objects_known_answers(gpu_lib, name, cls, rate, exact):
+    from simplefe_b200 import pydsp
+    x0 = _sine()
+    o = getattr(pydsp, cls)(F.taps("taps31"), 4, 128)   # libdsp/test/test_resample.py:17
+    if exact:
+        o.set_exact(True)
+    ys, cnt = [], []
+    for b in range(8):
+        n, y = o.process(x0[b * 128:(b + 1) * 128], 4 * 128, rate)   # test_resample.py:24
+        assert y.shape == (512,)
+        ys.append(y[:n])
+        cnt.append(n)
+    y = np.concatenate(ys)
+    assert cnt == list(KNOWN[name + "_counts"]), "output counts per call are bit-exact"
+    ref = KNOWN[name + "_y"]
+    if exact:
+        assert np.array_equal(y, ref), "exact mode reproduces the reference bit for bit"
+    else:
+        nrms, peak = F.err_metrics(y, ref)
+        assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
+
+
+def test_polyphase_arg_errors(gpu_lib, capfd):
+    from simplefe_b200 import pydsp
+    d = pydsp.decimate(F.taps("taps31"), 4, 128)
+    x = np.zeros(128, np.float32)
+    assert d.process(x, 512, 0.5)[0] == 0                              # decimate.cxx:75-78
+    assert d.process(np.zeros(129, np.float32), 512, 2.0)[0] == 0      # decimate.cxx:79-82
+    assert d.process(x, 10, 2.0)[0] == 0                               # decimate.cxx:84-87
+    r = pydsp.resample(F.taps("taps31"), 4, 128)
+    assert r.process(x, 512, 0.2)[0] == 0                              # resample.cxx:91-94
+    out = capfd.readouterr().out
+    assert "rate should be larger than 1.0" in out and "output buffer is not large enough" in out
+
+
+@pytest.mark.parametrize("cls,up,rate,blk,tapname", [("decimate", 1, 8.0, 4096, "dec128"), ("decimate", 3, 208.33333, 1000, "rs512_l3"),
+                                                     ("decimate", 4, 2.5003, 777, "taps31"), ("resample", 4, 0.77, 128, "taps31"),
+                                                     ("resample", 24, 26.041666, 4096, "rs512_l24"), ("resample", 4, 1.77, 7, "taps31")])
+def test_polyphase_objects_random_vs_oracle(gpu_lib, oracle_lib, cls, up, rate, blk, tapname):
+    """ragged block sizes, fractional rates (mu != 0, held-over outputs), exact mode -> bit-exact"""
+    from oracle import oracle as O
+    from simplefe_b200 import pydsp
+    rng = np.random.default_rng(5)
+    x = rng.normal(0, 0.3, 20011).astype(np.float32)
+    t = F.taps(tapname)
+    ref = getattr(O, cls.capitalize())(t, up, blk, lib=oracle_lib).stream(x, rate)
+    g = getattr(pydsp, cls)(t, up, blk).set_exact(True)
+    out_len = int(np.floor(np.float32(blk) / np.float32(rate))) + 2
+    ys = []
+    for off in range(0, len(x), blk):
+        n, y = g.process(x[off:off + blk], out_len, rate)
+        ys.append(y[:n])
+    got = np.concatenate(ys)
+    assert len(got) == len(ref)
+    assert np.array_equal(got, ref)
+
+
+# ---- batched chain API ----------------------------------------------------------------------------
+
+def _chain(cfg, flags=0, S=None):
+    from simplefe_b200.chain import Chain
+    return Chain(S or cfg["S"], cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), flags=flags)
+
+
+@pytest.mark.parametrize("name", ["cfg1_small", "cfg2_small", "cfg3_small", "cfg4_small", "cfg5_small"])
+@pytest.mark.parametrize("flags", [0, 2, 1])
+def test_chain_vs_golden(gpu_lib, name, flags):
+    """small cases of every BASELINE config against the committed reference outputs (tests/golden/chain.npz);
+    flags: 0 = default plan (fused where possible), 2 = NO_FUSE (FFT blkconv + separate stages), 1 = EXACT"""
+    cfg = F.CONFIGS[name]
+    iq = F.make_input(cfg)
+    ch = _chain(cfg, flags)
+    got = ch.process(iq)
+    ref = CHAIN[name]
+    assert got.shape == ref.shape, (got.shape, ref.shape, ch.plan)
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
+    if flags == 1 and cfg.get("blkconv") is None:
+        assert np.array_equal(got, ref), "EXACT plan without FFT stage is bit-exact"
+
+
+@pytest.mark.parametrize("name", ["cfg2_small", "cfg5_small", "cfg1_small"])
+def test_chain_chunk_invariance(gpu_lib, name):
+    """integral-step configs: any split of the stream into calls gives the same concatenated output"""
+    cfg = F.CONFIGS[name]
+    iq = F.make_input(cfg)
+    one = _chain(cfg).process(iq)
+    ch = _chain(cfg)
+    parts, off = [], 0
+    for n in (1, 7, 1000, 4096, 12345, 3, 10 ** 9):
+        n = min(n, cfg["N"] - off)
+        if n <= 0:
+            break
+        parts.append(ch.process(iq[:, off:off + n]))
+        off += n
+    many = np.concatenate(parts, axis=1)
+    assert many.shape == one.shape
+    nrms, peak = F.err_metrics(many, one)
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
+
+
+def test_chain_int16_conversion_bit_exact(gpu_lib):
+    """a 1-tap unit filter exposes the in-kernel conversion: must equal (float)s * (1.0f/32767.0f) exactly"""
+    from simplefe_b200.chain import Chain
+    s = np.arange(-32768, 32768, dtype=np.int32).astype(np.int16)
+    iq = np.stack([s, s[::-1]], axis=1)[None]
+    ch = Chain(1, F.IN_I16, None, dict(klass=1, taps=np.array([1.0], np.float32), up=1, blk=4096, rate=1.0), flags=1)
+    got = ch.process(iq)[0]
+    want = (iq[0].astype(np.float32) * np.float32(1.0 / 32767.0)).view(np.complex64)[:, 0]
+    assert np.array_equal(got, want)
+    u = np.arange(256, dtype=np.uint8)
+    iq8 = np.stack([u, u[::-1]], axis=1)[None]
+    ch8 = Chain(1, F.IN_U8, None, dict(klass=1, taps=np.array([1.0], np.float32), up=1, blk=4096, rate=1.0), flags=1)
+    want8 = ((iq8[0].astype(np.int32) - 128).astype(np.float32) * np.float32(1.0 / 127.0)).view(np.complex64)[:, 0]
+    assert np.array_equal(ch8.process(iq8)[0], want8)
+
+
+def test_chain_linearity_full_size_stream(gpu_lib):
+    """size-independent property at BASELINE length (2^20 samples/stream): chain(a) + chain(b) == chain(a+b)"""
+    cfg = dict(F.CONFIGS["cfg5"], S=2)
+    rng = np.random.default_rng(99)
+    a = rng.integers(-8000, 8000, size=(2, cfg["N"], 2)).astype(np.int16)
+    b = rng.integers(-8000, 8000, size=(2, cfg["N"], 2)).astype(np.int16)
+    ya, yb, yab = (_chain(cfg, S=2).process(v) for v in (a, b, (a + b).astype(np.int16)))
+    assert ya.shape[1] == 5034 or ya.shape[1] == 5033
+    nrms, peak = F.err_metrics(ya + yb, yab)
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
+
+
+def test_chain_dev_pointers_and_streams(gpu_lib, oracle_lib):
+    """device-resident entry point on a caller-provided CUDA stream (torch only supplies memory and the stream)"""
+    import torch
+    from oracle import oracle as O
+    cfg = dict(F.CONFIGS["cfg5_small"], S=5)
+    iq = F.make_input(cfg)
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg["blkconv"], cfg["stage_a"], cfg["stage_b"], lib=oracle_lib)
+    ch = _chain(cfg)
+    d_in = torch.from_numpy(iq).cuda()
+    cap = ch.max_out(cfg["N"])
+    d_out = torch.zeros((cfg["S"], cap, 2), dtype=torch.float32, device="cuda")
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        n = ch.process_dev(d_in.data_ptr(), cfg["N"], cfg["N"], d_out.data_ptr(), cap, st.cuda_stream)
+    st.synchronize()
+    got = d_out.cpu().numpy()[:, :n].view(np.complex64)[..., 0]
+    assert got.shape == ref.shape
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
+
+
+def test_empty_and_tiny_inputs(gpu_lib):
+    cfg = F.CONFIGS["cfg5_small"]
+    ch = _chain(cfg)
+    iq = F.make_input(dict(cfg, N=5))
+    y = ch.process(iq[:, :0])
+    assert y.shape == (cfg["S"], 0)
+    y = ch.process(iq)          # 5 samples: one decimated sample, one resampled output
+    assert y.shape[1] in (0, 1)
+
+
+def test_dac10_packing(gpu_lib):
+    """float -> 10-bit DAC words, examples/bpsk/bpsk.cxx:76-101, integer exact"""
+    import torch
+    rng = np.random.default_rng(1)
+    x = np.concatenate([rng.uniform(-1, 1, 4096), [1.0, -1.0, 0.0, 0.999]]).astype(np.float32)
+    u = ((x * np.float32(511)).astype(np.int16).astype(np.int32) + 512) & 0x3FF
+    u = u.reshape(-1, 4)
+    want = np.stack([(u[:, 0] >> 8) | ((u[:, 1] >> 8) << 2) | ((u[:, 2] >> 8) << 4) | ((u[:, 3] >> 8) << 6),
+                     u[:, 0] & 0xFF, u[:, 1] & 0xFF, u[:, 2] & 0xFF, u[:, 3] & 0xFF], axis=1).astype(np.uint8)
+    d_in = torch.from_numpy(x).cuda()
+    d_out = torch.zeros(len(x) // 4 * 5, dtype=torch.uint8, device="cuda")
+    assert gpu_lib.sfe_pack_dac10_dev(d_in.data_ptr(), len(x), d_out.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy().reshape(-1, 5), want)
