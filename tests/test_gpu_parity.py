@@ -169,12 +169,13 @@ def test_chain_int16_conversion_bit_exact(gpu_lib):
     ch = Chain(1, F.IN_I16, None, dict(klass=1, taps=np.array([1.0], np.float32), up=1, blk=4096, rate=1.0), flags=1)
     got = ch.process(iq)[0]
     want = (iq[0].astype(np.float32) * np.float32(1.0 / 32767.0)).view(np.complex64)[:, 0]
-    assert np.array_equal(got, want)
+    # rate 1.0: the last sample's interpolation partner is in the next call, so the reference holds it over
+    assert len(got) == len(want) - 1 and np.array_equal(got, want[:-1])
     u = np.arange(256, dtype=np.uint8)
     iq8 = np.stack([u, u[::-1]], axis=1)[None]
     ch8 = Chain(1, F.IN_U8, None, dict(klass=1, taps=np.array([1.0], np.float32), up=1, blk=4096, rate=1.0), flags=1)
     want8 = ((iq8[0].astype(np.int32) - 128).astype(np.float32) * np.float32(1.0 / 127.0)).view(np.complex64)[:, 0]
-    assert np.array_equal(ch8.process(iq8)[0], want8)
+    assert np.array_equal(ch8.process(iq8)[0], want8[:-1])
 
 
 def test_chain_linearity_full_size_stream(gpu_lib):
