@@ -29,7 +29,7 @@ using namespace sfe;
 
 namespace {
 
-enum OpKind { OP_BLKCONV, OP_DECIM, OP_POLY };
+enum OpKind { OP_BLKCONV, OP_DECIM, OP_POLY, OP_TOEP };
 
 struct Op {
     OpKind kind;
@@ -51,6 +51,9 @@ struct Op {
     // decimating FIR
     int D = 0, QLP = 0;
     float *d_gp = nullptr;
+    // tensor-core Toeplitz FIR
+    ToepHost toep;
+    int8_t *d_bmat = nullptr;
     // per call
     long n_in = 0, n_out = 0;
     std::string name;
@@ -115,6 +118,17 @@ bool make_decim(Op &op, const std::vector<double> &g, int D)
     return upload(&op.d_gp, gp);
 }
 
+bool make_toep(Op &op, const std::vector<double> &g)
+{
+    if (!toeplitz_prepare(g, op.toep)) return false;
+    op.kind = OP_TOEP;
+    op.D = 8;
+    op.T = (int)g.size();
+    op.H = op.T + op.D;
+    return SFE_CUDA(cudaMalloc(&op.d_bmat, op.toep.bmat.size())) &&
+           SFE_CUDA(cudaMemcpy(op.d_bmat, op.toep.bmat.data(), op.toep.bmat.size(), cudaMemcpyHostToDevice));
+}
+
 bool alloc_hist(Op &op, int S)
 {
     const size_t bytes = (size_t)S * op.H * fmt_bytes(op.in_fmt);
@@ -126,7 +140,7 @@ bool alloc_hist(Op &op, int S)
 long stage_max_out(const Op &op, long n)
 {
     if (op.kind == OP_BLKCONV) return n;
-    const double r = op.kind == OP_DECIM ? (double)op.D : (double)op.rate;
+    const double r = (op.kind == OP_DECIM || op.kind == OP_TOEP) ? (double)op.D : (double)op.rate;
     const long calls = op.blk > 0 ? (n + op.blk - 1) / op.blk : 1;
     return (long)((double)n / r) + 2 * calls + 4;
 }
@@ -216,6 +230,21 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             // uniform phase-0 schedule: positions are multiples of `up` (or -1 when up == 1)
             p.n_first = op.sched.pos0 >= 0 ? op.sched.pos0 / op.up : -1;
             rc = launch_decim_fir(p, st);
+        } else if (op.kind == OP_TOEP && op.n_out > 0) {
+            ToepParams p{};
+            p.in = in;
+            p.out = static_cast<float2 *>(dst);
+            p.out_pitch = dst_pitch;
+            p.n_streams = ns;
+            p.n_out = op.n_out;
+            p.n_first = op.sched.pos0 >= 0 ? op.sched.pos0 / op.up : -1;
+            p.KB = op.toep.KB;
+            p.bmat = op.d_bmat;
+            for (int t = 0; t < 3; t++) {
+                p.w[t] = op.toep.w[t];
+                p.corr[t] = op.toep.corr[t];
+            }
+            rc = launch_toeplitz(p, st);
         } else if (op.kind == OP_POLY && op.n_out > 0) {
             PolyParams p{};
             p.in = in;
@@ -354,7 +383,13 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
             } else {
                 c->plan += "decim_fir";
             }
-            ok = ok && make_decim(op, g, (int)(step / s.up));
+            const bool tensor = !(d->flags & SFE_FLAG_NO_TENSOR) && fmt == SFE_IN_I16 && step / s.up == 8 &&
+                                d->n_streams >= 8 && (int)g.size() <= toeplitz_max_taps();
+            if (tensor && make_toep(op, g)) {
+                c->plan += "[toeplitz_i8_tcgen05]";
+            } else {
+                ok = ok && make_decim(op, g, (int)(step / s.up));
+            }
             c->plan += "/D" + std::to_string(op.D) + "T" + std::to_string(op.T);
         } else {
             op.kind = OP_POLY;
@@ -387,6 +422,7 @@ extern "C" void sfe_chain_destroy(sfe_chain *c)
         cudaFree(op.hp);
         cudaFree(op.d_taps);
         cudaFree(op.d_gp);
+        cudaFree(op.d_bmat);
         cudaFree(op.d_sched);
     }
     for (Workspace &w : c->ws) {

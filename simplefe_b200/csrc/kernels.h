@@ -55,6 +55,31 @@ struct DecimParams {
 };
 int launch_decim_fir(const DecimParams &p, cudaStream_t st);
 
+// ---- K2t: decimate-by-8 FIR as an int8 Toeplitz contraction on tcgen05 (toeplitz_mma_kernel.cu) ---
+struct ToepParams {
+    StreamView in;        // int16 IQ rows
+    float2 *out;
+    long out_pitch;
+    int n_streams;
+    long n_out;
+    long n_first;         // y[k] = sum_j g[j] x[n_first + 8k - j]
+    int KB;               // 128-byte K-blocks per window = ceil((T-1)/128) + 1
+    const int8_t *bmat;   // device image of the B operand tiles (toeplitz_prepare)
+    float w[3];           // digit weights (include max|g| / Zmax / 32767)
+    float corr[3];        // 128 * sum_j d_tau[j]
+    // filled by launch_toeplitz
+    int ring, n_groups;
+    long n_steps;
+};
+struct ToepHost {
+    int KB = 0;
+    float w[3] = {0, 0, 0}, corr[3] = {0, 0, 0};
+    std::vector<int8_t> bmat;
+};
+bool toeplitz_prepare(const std::vector<double> &g, ToepHost &h);
+int toeplitz_max_taps();
+int launch_toeplitz(const ToepParams &p, cudaStream_t st);
+
 // ---- small utilities (util_kernels.cu) -----------------------------------------------------------
 // hist_new[s][0..H) <- last H samples of (hist_old ++ cur[0..n)) for every stream row; elem = bytes per sample
 int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long pitch, long n, int H, int elem, int n_streams,

@@ -1,0 +1,355 @@
+// toeplitz_mma_kernel.cu -- K2t: decimate-by-8 FIR over many int16 IQ streams that share one filter,
+// as a Toeplitz-batched dense contraction on the 5th-generation tensor cores (tcgen05, int8).
+//
+//   y[s][k] = sum_j g[j] * x[s][n_first + 8k - j]           (g: up to 641 taps; x: int16 I/Q)
+//
+// This is the reference's blkconv -> decimate pair for the many-streams case (blkconv.cxx:77-110 and
+// decimate.cxx:102-140 with rate 8, upsample 1), with the two FIRs pre-convolved into g (chain.cu).
+//
+// Exact integer formulation.  Every int16 sample is the byte pair (lo unsigned, hi signed): s = 256*hi + lo.
+// The hi byte is biased to unsigned (hi ^ 0x80 = hi + 128) so that all four byte planes of an IQ stream
+// (I_lo, I_hi, Q_lo, Q_hi) are u8 rows of the A operand.  The taps are quantised once to 24-bit fixed
+// point and split into three signed base-256 digits d0, d1, d2 (s8), which form the B operand:
+//   B[kappa][(tau, o)] = d_tau[128*(KB-1) + 8*o - kappa]       (a banded Toeplitz block, 16 outputs o per step)
+// One tile step covers 128 input samples of 32 streams: M = 128 rows (32 streams x 4 byte planes),
+// N = 48 columns (3 digits x 16 outputs), K = 128*KB window bytes, accumulated in int32 in TMEM -- the
+// arithmetic is exact; the only approximation is the 2^-23 (relative to the largest tap) tap quantisation.
+// The epilogue recombines  y = sum_tau w_tau * (256*(A_hi - 128*sum d_tau) + A_lo)  in fp32.
+//
+// Persistent, warp-specialised CTA (one per SM):
+//   warps 0-3  epilogue   tcgen05.ld of the int32 accumulators, digit/byte recombination, float2 stores
+//   warp  4    MMA issue  one thread; tcgen05.mma.cta_group::1.kind::i8, commits to mbarriers
+//   warps 5-12 producers  128-bit global loads of int16 IQ, byte-plane split with PRMT, stores into the
+//                         K-major SWIZZLE_128B operand tiles of a shared-memory ring (no im2col copy:
+//                         consecutive steps reuse KB-1 of their KB K-block tiles)
+#include "kernels.h"
+
+namespace sfe {
+
+namespace {
+
+constexpr int TD = 8;              // decimation
+constexpr int TNO = 128 / TD;      // outputs per tile step and row
+constexpr int TNT = 3;             // tap digits
+constexpr int TNCOL = TNT * TNO;   // 48 accumulator columns
+constexpr int TILE_BYTES = 128 * 128;
+constexpr int N_EPI_WARPS = 4, N_PROD_WARPS = 8;
+constexpr int N_THREADS = 32 * (N_EPI_WARPS + 1 + N_PROD_WARPS);
+constexpr int MAX_RING = 12;
+constexpr int ACC_STRIDE = 64;     // TMEM columns between the two accumulators
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}\n" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// K-major SWIZZLE_128B operand tile: rows 128 B apart, 8-row groups 1024 B apart (SBO), descriptor version 1
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr)
+{
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)2 << 61);
+}
+__device__ __forceinline__ uint32_t swz(int row, int byte)  // byte offset inside a tile
+{
+    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((byte >> 4) ^ (row & 7)) << 4) | (byte & 15)));
+}
+
+struct Piece {
+    int g;
+    long j0, j1;
+};
+
+// the flat (group, step) range of this CTA, cut at group boundaries
+struct PieceIter {
+    long f, f1, J;
+    __device__ PieceIter(const ToepParams &p)
+    {
+        J = p.n_steps;
+        const long F = (long)p.n_groups * J;
+        const long W = (F + gridDim.x - 1) / gridDim.x;
+        f = (long)blockIdx.x * W;
+        f1 = f + W < F ? f + W : F;
+    }
+    __device__ bool next(Piece &pc)
+    {
+        if (f >= f1) return false;
+        pc.g = (int)(f / J);
+        pc.j0 = f - (long)pc.g * J;
+        const long left = f1 - f;
+        pc.j1 = pc.j0 + left < J ? pc.j0 + left : J;
+        f += pc.j1 - pc.j0;
+        return true;
+    }
+};
+
+__device__ __forceinline__ uint32_t load_i16(const ToepParams &p, int s, long n)
+{
+    if (s >= p.n_streams || n >= p.in.n) return 0u;
+    if (n >= 0) return __ldg(reinterpret_cast<const uint32_t *>(p.in.cur) + (long)s * p.in.pitch + n);
+    const long h = (long)p.in.H + n;
+    return h < 0 ? 0u : __ldg(reinterpret_cast<const uint32_t *>(p.in.hist) + (long)s * p.in.H + h);
+}
+
+__global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepParams p)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bar_full[MAX_RING], bar_empty[MAX_RING], bar_acc_full[2], bar_acc_empty[2];
+    __shared__ uint32_t tmem_base_s;
+
+    const int KB = p.KB, R = p.ring;
+    uint8_t *sbase = smem + ((1024u - (smem_u32(smem) & 1023u)) & 1023u);   // SWIZZLE_128B tiles need 1024 B alignment
+    uint8_t *sB = sbase;                                  // KB tiles of TNCOL rows x 128 B (swizzled image)
+    uint8_t *ring = sbase + ((KB * TNCOL * 128 + 1023) & ~1023);  // R tiles of 128 rows x 128 B
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    // ---- one-time setup ---------------------------------------------------------------------------
+    for (int i = tid; i < KB * TNCOL * 128 / 16; i += N_THREADS)
+        reinterpret_cast<uint4 *>(sB)[i] = __ldg(reinterpret_cast<const uint4 *>(p.bmat) + i);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (tid == 0) {
+        for (int i = 0; i < R; i++) {
+            mbar_init(&bar_full[i], 32 * N_PROD_WARPS);
+            mbar_init(&bar_empty[i], 1);
+        }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(&bar_acc_full[i], 1);
+            mbar_init(&bar_acc_empty[i], 32 * N_EPI_WARPS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == N_EPI_WARPS) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(128));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = tmem_base_s;
+
+    const long X0 = p.n_first - 128L * (KB - 1);          // first sample of K-block 0
+
+    if (warp > N_EPI_WARPS) {
+        // =================================== producers ==============================================
+        const int pw = warp - N_EPI_WARPS - 1;
+        const bool aligned = ((X0 & 3) == 0) && ((p.in.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.in.cur) & 15) == 0);
+        long fill = 0;
+        PieceIter it(p);
+        Piece pc;
+        while (it.next(pc)) {
+            const int s_base = pc.g * 32;
+            for (long m = pc.j0; m < pc.j1 + KB - 1; m++, fill++) {
+                const int slot = (int)(fill % R);
+                const uint32_t par = (uint32_t)((fill / R) & 1);
+                const long n0 = X0 + 128 * m + 4 * lane;   // this lane's 4 samples
+                uint4 v[4];
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int sl = pw + 8 * q, s = s_base + sl;
+                    if (aligned && s < p.n_streams && n0 >= 0 && n0 + 3 < p.in.n) {
+                        v[q] = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const uint32_t *>(p.in.cur) + (long)s * p.in.pitch + n0));
+                    } else {
+                        v[q].x = load_i16(p, s, n0);
+                        v[q].y = load_i16(p, s, n0 + 1);
+                        v[q].z = load_i16(p, s, n0 + 2);
+                        v[q].w = load_i16(p, s, n0 + 3);
+                    }
+                }
+                mbar_wait(&bar_empty[slot], par ^ 1);      // slot free (first pass falls through)
+                uint8_t *tile = ring + (size_t)slot * TILE_BYTES;
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int sl = pw + 8 * q;
+                    const uint32_t t01 = __byte_perm(v[q].x, v[q].y, 0x5140), t23 = __byte_perm(v[q].z, v[q].w, 0x5140);
+                    const uint32_t u01 = __byte_perm(v[q].x, v[q].y, 0x7362), u23 = __byte_perm(v[q].z, v[q].w, 0x7362);
+                    const uint32_t il = __byte_perm(t01, t23, 0x5410), ih = __byte_perm(t01, t23, 0x7632) ^ 0x80808080u;
+                    const uint32_t ql = __byte_perm(u01, u23, 0x5410), qh = __byte_perm(u01, u23, 0x7632) ^ 0x80808080u;
+                    const int r = 4 * sl;
+                    *reinterpret_cast<uint32_t *>(tile + swz(r + 0, 4 * lane)) = il;
+                    *reinterpret_cast<uint32_t *>(tile + swz(r + 1, 4 * lane)) = ih;
+                    *reinterpret_cast<uint32_t *>(tile + swz(r + 2, 4 * lane)) = ql;
+                    *reinterpret_cast<uint32_t *>(tile + swz(r + 3, 4 * lane)) = qh;
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(&bar_full[slot]);
+            }
+        }
+    } else if (warp == N_EPI_WARPS) {
+        // =================================== MMA issuer ==============================================
+        if (lane == 0) {
+            const uint32_t idesc = (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t)(TNCOL >> 3) << 17) | ((128u >> 4) << 24);
+            const uint32_t ring_a = smem_u32(ring), b_a = smem_u32(sB);
+            long fill = 0, step = 0;                       // K-blocks consumed / steps issued so far
+            PieceIter it(p);
+            Piece pc;
+            while (it.next(pc)) {
+                long ready = 0;                            // K-blocks of this piece known to be in the ring
+                for (long j = pc.j0; j < pc.j1; j++, step++) {
+                    const long need = (j - pc.j0) + KB;
+                    for (; ready < need; ready++) {
+                        const long fc = fill + ready;
+                        mbar_wait(&bar_full[fc % R], (uint32_t)((fc / R) & 1));
+                    }
+                    const int a = (int)(step & 1);
+                    mbar_wait(&bar_acc_empty[a], (uint32_t)(((step >> 1) & 1) ^ 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;");
+                    const uint32_t d_tmem = tmem + a * ACC_STRIDE;
+                    for (int kb = 0; kb < KB; kb++) {
+                        const int slot = (int)((fill + (j - pc.j0) + kb) % R);
+                        const uint32_t at = ring_a + slot * TILE_BYTES, bt = b_a + kb * (TNCOL * 128);
+#pragma unroll
+                        for (int ks = 0; ks < 4; ks++) {
+                            const uint64_t da = umma_desc(at + ks * 32), db = umma_desc(bt + ks * 32);
+                            const uint32_t acc = (kb | ks) ? 1u : 0u;
+                            asm volatile("{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+                                         " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n"
+                                         ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+                        }
+                    }
+                    umma_commit(&bar_acc_full[a]);                                   // accumulator ready
+                    umma_commit(&bar_empty[(fill + (j - pc.j0)) % R]);               // oldest K-block retired
+                }
+                // the KB-1 trailing K-blocks of the piece are not reused by the next piece
+                for (int t = 0; t < KB - 1; t++) umma_commit(&bar_empty[(fill + (pc.j1 - pc.j0) + t) % R]);
+                fill += (pc.j1 - pc.j0) + KB - 1;
+            }
+        }
+    } else {
+        // =================================== epilogue ================================================
+        const int plane = lane & 3;                        // 0 I_lo, 1 I_hi, 2 Q_lo, 3 Q_hi
+        const bool hi = plane & 1;
+        const float c0 = hi ? p.corr[0] : 0.f, c1 = hi ? p.corr[1] : 0.f, c2 = hi ? p.corr[2] : 0.f;
+        const float byte_w = hi ? 256.f : 1.f;
+        long step = 0;
+        PieceIter it(p);
+        Piece pc;
+        while (it.next(pc)) {
+            const int s = pc.g * 32 + warp * 8 + (lane >> 2);
+            for (long j = pc.j0; j < pc.j1; j++, step++) {
+                const int a = (int)(step & 1);
+                mbar_wait(&bar_acc_full[a], (uint32_t)((step >> 1) & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                uint32_t v[TNCOL];
+                const uint32_t ta = tmem + ((uint32_t)(warp * 32) << 16) + a * ACC_STRIDE;
+#pragma unroll
+                for (int c = 0; c < TNT; c++)
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                                 : "=r"(v[16 * c + 0]), "=r"(v[16 * c + 1]), "=r"(v[16 * c + 2]), "=r"(v[16 * c + 3]), "=r"(v[16 * c + 4]),
+                                   "=r"(v[16 * c + 5]), "=r"(v[16 * c + 6]), "=r"(v[16 * c + 7]), "=r"(v[16 * c + 8]), "=r"(v[16 * c + 9]),
+                                   "=r"(v[16 * c + 10]), "=r"(v[16 * c + 11]), "=r"(v[16 * c + 12]), "=r"(v[16 * c + 13]),
+                                   "=r"(v[16 * c + 14]), "=r"(v[16 * c + 15])
+                                 : "r"(ta + 16 * c));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;");
+                mbar_arrive(&bar_acc_empty[a]);            // TMEM buffer free for the step after next
+                float2 *o = p.out + (long)s * p.out_pitch + j * TNO;
+#pragma unroll
+                for (int i = 0; i < TNO; i++) {
+                    float f = p.w[0] * ((float)(int)v[i] - c0);
+                    f = fmaf(p.w[1], (float)(int)v[TNO + i] - c1, f);
+                    f = fmaf(p.w[2], (float)(int)v[2 * TNO + i] - c2, f);
+                    f *= byte_w;
+                    f += __shfl_xor_sync(0xffffffffu, f, 1);             // lo + 256*hi
+                    const float q = __shfl_down_sync(0xffffffffu, f, 2); // Q next to I
+                    if (plane == 0 && s < p.n_streams && j * TNO + i < p.n_out) o[i] = make_float2(f, q);
+                }
+            }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    __syncwarp();
+    if (warp == N_EPI_WARPS) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(128));
+}
+
+}  // namespace
+
+int toeplitz_max_taps() { return 128 * (MAX_RING - 4 - 1) + 1; }
+
+int launch_toeplitz(const ToepParams &p_in, cudaStream_t st)
+{
+    ToepParams p = p_in;
+    if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
+    p.n_groups = (p.n_streams + 31) / 32;
+    p.n_steps = (p.n_out + TNO - 1) / TNO;
+    p.ring = p.KB + 4 <= MAX_RING ? p.KB + 4 : MAX_RING;
+    if (p.KB < 1 || p.KB + 2 > MAX_RING || p.in.fmt != SFE_IN_I16) {
+        set_error("toeplitz_i8: unsupported configuration");
+        return SFE_ERR_ARG;
+    }
+    const size_t smem = ((size_t)(p.KB * TNCOL * 128 + 1023) & ~(size_t)1023) + (size_t)p.ring * TILE_BYTES + 1024;
+    if (!SFE_CUDA(cudaFuncSetAttribute(toeplitz_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
+    int dev = 0, sms = 0;
+    if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
+    const long F = (long)p.n_groups * p.n_steps;
+    long grid = F / 4 > 0 ? F / 4 : 1;                    // at least ~4 steps per CTA
+    if (grid > sms) grid = sms;
+    toeplitz_i8_kernel<<<(unsigned)grid, N_THREADS, smem, st>>>(p);
+    count_launch();
+    return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+}
+
+// Host side: quantise g to 24-bit fixed point, split into three signed base-256 digits and lay the banded
+// Toeplitz blocks out exactly as the kernel's shared-memory image (K-major, SWIZZLE_128B).
+bool toeplitz_prepare(const std::vector<double> &g, ToepHost &h)
+{
+    const int T = (int)g.size();
+    h.KB = (T - 1 + 127) / 128 + 1;
+    if (h.KB < 2) h.KB = 2;
+    double sigma = 0;
+    for (double v : g) sigma = fabs(v) > sigma ? fabs(v) : sigma;
+    if (!(sigma > 0)) sigma = 1.0;
+    const double Zmax = (double)((127 << 16) - (128 << 8) - 128);
+    std::vector<int> d0(T), d1(T), d2(T);
+    long sum[3] = {0, 0, 0};
+    for (int j = 0; j < T; j++) {
+        long Z = llround(g[j] / sigma * Zmax);
+        auto digit = [](long z) { long m = ((z + 128) % 256 + 256) % 256; return (int)(m - 128); };
+        d2[j] = digit(Z);
+        Z = (Z - d2[j]) / 256;
+        d1[j] = digit(Z);
+        Z = (Z - d1[j]) / 256;
+        d0[j] = (int)Z;
+        if (d0[j] < -128 || d0[j] > 127) return false;
+        sum[0] += d0[j];
+        sum[1] += d1[j];
+        sum[2] += d2[j];
+    }
+    const double Kq = sigma / Zmax / 32767.0;             // x = s/32767, folded into the weights
+    h.w[0] = (float)(Kq * 65536.0);
+    h.w[1] = (float)(Kq * 256.0);
+    h.w[2] = (float)Kq;
+    for (int t = 0; t < 3; t++) h.corr[t] = (float)(128 * sum[t]);   // bias of the hi ^ 0x80 rows, exact in fp32
+    h.bmat.assign((size_t)h.KB * TNCOL * 128, 0);
+    const std::vector<int> *dig[3] = {&d0, &d1, &d2};
+    for (int kb = 0; kb < h.KB; kb++)
+        for (int n = 0; n < TNCOL; n++) {
+            const int tau = n / TNO, o = n % TNO;
+            for (int c = 0; c < 128; c++) {
+                const int jt = 128 * (h.KB - 1) + TD * o - (128 * kb + c);
+                const int val = (jt >= 0 && jt < T) ? (*dig[tau])[jt] : 0;
+                const size_t off = (size_t)kb * TNCOL * 128 + (n >> 3) * 1024 + (n & 7) * 128 + ((((c >> 4) ^ (n & 7)) << 4) | (c & 15));
+                h.bmat[off] = (int8_t)val;
+            }
+        }
+    return true;
+}
+
+}  // namespace sfe

@@ -235,3 +235,45 @@ def test_dac10_packing(gpu_lib):
     assert gpu_lib.sfe_pack_dac10_dev(d_in.data_ptr(), len(x), d_out.data_ptr(), None) == 0
     torch.cuda.synchronize()
     assert np.array_equal(d_out.cpu().numpy().reshape(-1, 5), want)
+
+
+# ---- tensor-core Toeplitz path (needs >= 8 streams sharing one filter) ------------------------------
+
+@pytest.mark.parametrize("base,S,N", [("cfg5_small", 40, 70001), ("cfg2_small", 33, 50003), ("cfg5_small", 8, 4099)])
+def test_chain_tensor_path_vs_oracle(gpu_lib, oracle_lib, base, S, N):
+    from oracle import oracle as O
+    cfg = dict(F.CONFIGS[base], S=S, N=N)
+    iq = F.make_input(cfg)
+    iq[0, :100] = 32767          # full-scale corners of the byte-plane split
+    iq[1, :100] = -32768
+    iq[2, 100:300, 0] = -1
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=4)
+    ch = _chain(cfg)
+    assert "toeplitz_i8_tcgen05" in ch.plan, ch.plan
+    got = ch.process(iq)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
+    # and against the CUDA-core plan of the same chain
+    alt = _chain(cfg, flags=4).process(iq)
+    nrms, peak = F.err_metrics(got, alt)
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
+
+
+def test_chain_tensor_path_chunk_invariance(gpu_lib):
+    cfg = dict(F.CONFIGS["cfg5_small"], S=9, N=40000)
+    iq = F.make_input(cfg)
+    one = _chain(cfg).process(iq)
+    ch = _chain(cfg)
+    assert "toeplitz_i8_tcgen05" in ch.plan
+    parts, off = [], 0
+    for n in (1, 7, 1000, 4096, 12345, 3, 10 ** 9):
+        n = min(n, cfg["N"] - off)
+        if n <= 0:
+            break
+        parts.append(ch.process(iq[:, off:off + n]))
+        off += n
+    many = np.concatenate(parts, axis=1)
+    assert many.shape == one.shape
+    nrms, peak = F.err_metrics(many, one)
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
