@@ -91,7 +91,8 @@ enum { SFE_KLASS_NONE = 0, SFE_KLASS_DECIMATE = 1, SFE_KLASS_RESAMPLE = 2 };
 enum {
     SFE_FLAG_EXACT = 1,        /* polyphase stages in reference operation order (slow path)        */
     SFE_FLAG_NO_FUSE = 2,      /* run blkconv and stage A as separate kernels even when fusable    */
-    SFE_FLAG_NO_TENSOR = 4     /* never use the tensor-core Toeplitz kernel                        */
+    SFE_FLAG_NO_TENSOR = 4,    /* never use the tensor-core Toeplitz kernel                        */
+    SFE_FLAG_NO_BANK = 8       /* never fold the whole chain into one polyphase bank (K3)          */
 };
 
 typedef struct {

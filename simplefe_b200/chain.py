@@ -10,7 +10,7 @@ from ._lib import ChainDesc, SfeError, check, last_error, lib, _f32p
 
 IN_I16, IN_U8, IN_F32 = 0, 1, 2
 KLASS_NONE, KLASS_DECIMATE, KLASS_RESAMPLE = 0, 1, 2
-FLAG_EXACT, FLAG_NO_FUSE, FLAG_NO_TENSOR = 1, 2, 4
+FLAG_EXACT, FLAG_NO_FUSE, FLAG_NO_TENSOR, FLAG_NO_BANK = 1, 2, 4, 8
 _NP_DT = {IN_I16: np.int16, IN_U8: np.uint8, IN_F32: np.float32}
 BYTES_PER_SAMPLE = {IN_I16: 4, IN_U8: 2, IN_F32: 8}
 

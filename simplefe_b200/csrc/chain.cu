@@ -14,6 +14,7 @@
 // be fed in arbitrary pieces.
 #include <cmath>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -29,7 +30,7 @@ using namespace sfe;
 
 namespace {
 
-enum OpKind { OP_BLKCONV, OP_DECIM, OP_POLY, OP_TOEP };
+enum OpKind { OP_BLKCONV, OP_DECIM, OP_POLY, OP_TOEP, OP_BANK };
 
 struct Op {
     OpKind kind;
@@ -54,6 +55,18 @@ struct Op {
     // tensor-core Toeplitz FIR
     ToepHost toep;
     int8_t *d_bmat = nullptr;
+    // fused bank (K3): optional pre-stage (blkconv and/or integral decimator) folded into the bank stage's taps
+    bool has_pre = false;
+    int pre_up = 1, pre_blk = 0;
+    float pre_rate = 1.f;
+    WalkState pre_ws;
+    Schedule pre_sched;
+    std::vector<double> g;         // pre-stage FIR at the raw rate (double)
+    std::vector<float> r;          // bank stage taps as the reference ctor pads them
+    std::map<int, float *> d_tables;  // bank tables by alignment key (bank_table)
+    int row_len = 0, n_rows = 0, rows_per_phase = 1;
+    long n_first = 0;
+    bool bad_sched = false;
     // per call
     long n_in = 0, n_out = 0;
     std::string name;
@@ -65,6 +78,8 @@ struct Workspace {
     std::vector<size_t> mid_bytes;
     void *d_in = nullptr, *d_out = nullptr;  // staging for process_host
     size_t in_bytes = 0, out_bytes = 0;
+    void *d_align = nullptr;                 // realigned copy of caller rows that TMA cannot address
+    size_t align_bytes = 0;
     cudaStream_t st = nullptr;
 };
 
@@ -140,6 +155,14 @@ bool alloc_hist(Op &op, int S)
 long stage_max_out(const Op &op, long n)
 {
     if (op.kind == OP_BLKCONV) return n;
+    if (op.kind == OP_BANK) {
+        if (op.has_pre) {
+            const long calls = (n + op.pre_blk - 1) / op.pre_blk;
+            n = (long)((double)n / op.D) + 2 * calls + 4;
+        }
+        const long calls = (n + op.blk - 1) / op.blk;
+        return (long)((double)n / (double)op.rate) + 2 * calls + 4;
+    }
     const double r = (op.kind == OP_DECIM || op.kind == OP_TOEP) ? (double)op.D : (double)op.rate;
     const long calls = op.blk > 0 ? (n + op.blk - 1) / op.blk : 1;
     return (long)((double)n / r) + 2 * calls + 4;
@@ -164,6 +187,21 @@ void plan_call(sfe_chain *c, long n_in)
         op.n_in = n;
         if (op.kind == OP_BLKCONV) {
             op.n_out = n;
+        } else if (op.kind == OP_BANK) {
+            long na = n;
+            op.n_first = 0;
+            op.bad_sched = false;
+            if (op.has_pre) {
+                walk_batch(op.pre_ws, op.pre_up, op.pre_blk, op.pre_rate, n, op.pre_sched);
+                na = (long)op.pre_sched.e.size();
+                if (na > 0) {
+                    op.bad_sched = !op.pre_sched.uniform || op.pre_sched.step != (int64_t)op.D * op.pre_up;
+                    op.n_first = op.pre_sched.pos0 >= 0 ? op.pre_sched.pos0 / op.pre_up : -1;
+                }
+            }
+            walk_batch(op.ws, op.up, op.blk, op.rate, na, op.sched);
+            op.n_out = (long)op.sched.e.size();
+            if (op.n_out > 0 && !op.sched.uniform) op.bad_sched = true;
         } else {
             walk_batch(op.ws, op.up, op.blk, op.rate, n, op.sched);
             op.n_out = (long)op.sched.e.size();
@@ -245,6 +283,48 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
                 p.corr[t] = op.toep.corr[t];
             }
             rc = launch_toeplitz(p, st);
+        } else if (op.kind == OP_BANK && op.n_out > 0) {
+            if (op.bad_sched) {
+                set_error("fused bank: the output schedule of this call is not uniform (float32 time walk lost exactness)");
+                return SFE_ERR_ARG;
+            }
+            // TMA needs 16-byte aligned rows: realign caller buffers that are not
+            if ((reinterpret_cast<uintptr_t>(src) & 15) || (src_pitch & 3)) {
+                const long ap = (op.n_in + 3) & ~3L;
+                if (!ensure(&w.d_align, &w.align_bytes, (size_t)ns * ap * 4)) return SFE_ERR_CUDA;
+                if (!SFE_CUDA(cudaMemcpy2DAsync(w.d_align, (size_t)ap * 4, src, (size_t)src_pitch * 4, (size_t)op.n_in * 4, ns,
+                                                cudaMemcpyDeviceToDevice, st)))
+                    return SFE_ERR_CUDA;
+                in.cur = w.d_align;
+                in.pitch = ap;
+            }
+            const int key = op.rows_per_phase == 4 ? -1 : (int)(op.n_first & 3);
+            auto it = op.d_tables.find(key);
+            if (it == op.d_tables.end()) {
+                std::vector<float> rows;
+                int rl = 0, nr = 0, tc = 0;
+                bank_table(op.g, op.D, op.r, op.up, (double)(1.0f / 32767.0f), key, rows, &rl, &nr, &tc);
+                float *d = nullptr;
+                if (!upload(&d, rows)) return SFE_ERR_CUDA;
+                it = op.d_tables.emplace(key, d).first;
+            }
+            BankParams p{};
+            p.in = in;
+            p.out = static_cast<float2 *>(dst);
+            p.out_pitch = dst_pitch;
+            p.n_streams = ns;
+            p.n_out = op.n_out;
+            p.pos0 = op.sched.pos0;
+            p.step = op.sched.step;
+            p.L = op.up;
+            p.D = op.D;
+            p.n_first = op.n_first;
+            p.H = op.H;
+            p.table = it->second;
+            p.row_len = op.row_len;
+            p.n_rows = op.n_rows;
+            p.rows_per_phase = op.rows_per_phase;
+            rc = launch_bank(p, st);
         } else if (op.kind == OP_POLY && op.n_out > 0) {
             PolyParams p{};
             p.in = in;
@@ -339,7 +419,61 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
     const bool a_decim = has_a && integral_step(d->a, &step_a) && step_a % d->a.up == 0 && !(d->flags & SFE_FLAG_EXACT);
     const bool fuse = has_bc && a_decim && !(d->flags & SFE_FLAG_NO_FUSE);
 
-    if (has_bc && !fuse) {
+    // ---- plan K3: the whole chain as one polyphase bank over the raw samples -------------------------------
+    // needs: int16 input, a last stage with an integral multi-phase step, and before it nothing but FIRs that
+    // keep every D-th sample (blkconv and/or an integral decimator).  Everything else uses the staged plans.
+    bool bank = false;
+    if (!(d->flags & (SFE_FLAG_EXACT | SFE_FLAG_NO_BANK)) && d->in_fmt == SFE_IN_I16 && has_a && (!has_b || a_decim)) {
+        const sfe_stage_desc &bs = has_b ? d->b : d->a;
+        long step_b = 0;
+        if (integral_step(bs, &step_b) && step_b % bs.up != 0) {
+            Op op{};
+            op.kind = OP_BANK;
+            op.in_fmt = fmt;
+            op.up = bs.up;
+            op.blk = bs.blk;
+            op.rate = bs.rate;
+            op.r = padded_taps(bs);
+            op.D = 1;
+            op.g.assign(1, 1.0);
+            if (has_b) {
+                op.has_pre = true;
+                op.pre_up = d->a.up;
+                op.pre_blk = d->a.blk;
+                op.pre_rate = d->a.rate;
+                op.D = (int)(step_a / d->a.up);
+                const std::vector<float> ta = padded_taps(d->a);
+                op.g.clear();
+                for (size_t q = 0; q * d->a.up < ta.size(); q++) op.g.push_back((double)ta[q * d->a.up]);
+                while (op.g.size() > 1 && op.g.back() == 0.0) op.g.pop_back();
+            }
+            if (has_bc) {
+                std::vector<double> f(op.g.size() + d->bc_ntaps - 1, 0.0);
+                for (size_t i = 0; i < op.g.size(); i++)
+                    for (int j = 0; j < d->bc_ntaps; j++) f[i + j] += op.g[i] * (double)d->bc_taps[j];
+                op.g.swap(f);
+            }
+            const int J = ((int)op.r.size() + op.up - 1) / op.up;
+            const int Tc = op.D * (J - 1) + (int)op.g.size();
+            const int NC = (Tc + 6) / 4;
+            op.row_len = 4 * NC;
+            op.rows_per_phase = op.D % 4 == 0 ? 1 : 4;
+            op.n_rows = op.up * op.rows_per_phase;
+            const long spacing = (long)op.D * (step_b / op.up);          // samples between consecutive outputs, at least
+            const long live = spacing >= 8 ? (NC - 1) / (spacing / 4) + 1 : 1 << 30;
+            if (live <= bank_max_live() && bank_smem_bytes(op.n_rows, op.row_len) <= 227 * 1024) {
+                op.H = (op.row_len + 2 * op.D + 4 + 31) / 32 * 32;
+                op.name = std::string("bank_fused(") + (has_bc ? "blkconv*" : "") + (has_b ? "decim*" : "") + "polyphase)/L" +
+                          std::to_string(op.up) + "D" + std::to_string(op.D) + "T" + std::to_string(Tc);
+                c->plan = op.name;
+                c->ops.push_back(op);
+                bank = true;
+            }
+        }
+    }
+    const bool staged = !bank;
+
+    if (staged && has_bc && !fuse) {
         Op op{};
         op.kind = OP_BLKCONV;
         op.in_fmt = fmt;
@@ -356,7 +490,7 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
         c->plan += op.name;
         fmt = SFE_IN_F32;
     }
-    for (int which = 0; which < 2 && ok; which++) {
+    for (int which = 0; which < 2 && ok && staged; which++) {
         const sfe_stage_desc &s = which == 0 ? d->a : d->b;
         if (s.klass == SFE_KLASS_NONE) continue;
         Op op{};
@@ -424,8 +558,10 @@ extern "C" void sfe_chain_destroy(sfe_chain *c)
         cudaFree(op.d_gp);
         cudaFree(op.d_bmat);
         cudaFree(op.d_sched);
+        for (auto &kv : op.d_tables) cudaFree(kv.second);
     }
     for (Workspace &w : c->ws) {
+        cudaFree(w.d_align);
         for (void *m : w.mid) cudaFree(m);
         cudaFree(w.d_in);
         cudaFree(w.d_out);
@@ -440,6 +576,7 @@ extern "C" int sfe_chain_reset(sfe_chain *c)
     if (!SFE_CUDA(cudaSetDevice(c->dev)) || !SFE_CUDA(cudaDeviceSynchronize())) return SFE_ERR_CUDA;
     for (Op &op : c->ops) {
         op.ws = WalkState{};
+        op.pre_ws = WalkState{};
         const size_t bytes = (size_t)c->S * op.H * fmt_bytes(op.in_fmt);
         for (int i = 0; i < 2; i++)
             if (!SFE_CUDA(cudaMemset(op.hist[i], 0, bytes))) return SFE_ERR_CUDA;
@@ -529,6 +666,7 @@ extern "C" int sfe_chain_process_host(sfe_chain *c, const void *h_in, long n_in,
     const int eb = fmt_bytes(c->in_fmt);
     // stream groups of ~64 MiB input: H2D(g+1) overlaps kernels(g) overlaps D2H(g-1) on two CUDA streams
     const size_t row_in = (size_t)n_in * eb;
+    const long dpitch = (n_in + 7) & ~7L;   // device staging rows start 16-byte aligned in every format (TMA)
     int gs = (int)((64u << 20) / (row_in ? row_in : 1));
     if (gs < 1) gs = 1;
     if (gs > c->S) gs = c->S;
@@ -541,13 +679,13 @@ extern "C" int sfe_chain_process_host(sfe_chain *c, const void *h_in, long n_in,
     for (int s0 = 0; s0 < c->S; s0 += gs, g++) {
         Workspace &w = c->ws[g & 1];
         const int ns = c->S - s0 < gs ? c->S - s0 : gs;
-        if (!ensure(&w.d_in, &w.in_bytes, (size_t)gs * row_in) ||
+        if (!ensure(&w.d_in, &w.in_bytes, (size_t)gs * dpitch * eb) ||
             !ensure(&w.d_out, &w.out_bytes, sizeof(float2) * (size_t)gs * opitch))
             return SFE_ERR_CUDA;
         const char *src = static_cast<const char *>(h_in) + (size_t)s0 * in_pitch * eb;
-        if (!SFE_CUDA(cudaMemcpy2DAsync(w.d_in, row_in, src, (size_t)in_pitch * eb, row_in, ns, cudaMemcpyHostToDevice, w.st)))
+        if (!SFE_CUDA(cudaMemcpy2DAsync(w.d_in, (size_t)dpitch * eb, src, (size_t)in_pitch * eb, row_in, ns, cudaMemcpyHostToDevice, w.st)))
             return SFE_ERR_CUDA;
-        rc = run_ops(c, w, s0, ns, w.d_in, n_in, w.d_out, opitch, w.st);
+        rc = run_ops(c, w, s0, ns, w.d_in, dpitch, w.d_out, opitch, w.st);
         if (rc != SFE_OK) return rc;
         if (no > 0) {
             char *dst = static_cast<char *>(h_out) + sizeof(float2) * (size_t)s0 * out_pitch;

@@ -80,6 +80,30 @@ bool toeplitz_prepare(const std::vector<double> &g, ToepHost &h);
 int toeplitz_max_taps();
 int launch_toeplitz(const ToepParams &p, cudaStream_t st);
 
+// ---- K3: fused polyphase bank over many int16 IQ streams (fused_bank_kernel.cu) ------------------
+// y[k] = sum_u c_ph[u] x[R_k - u];  pos = pos0 + k*step, M = floor(pos/L), ph = pos mod L, R_k = n_first + D*M
+struct BankParams {
+    StreamView in;        // int16 IQ rows, 16-byte aligned, pitch % 4 == 0; history of H samples
+    float2 *out;
+    long out_pitch;
+    int n_streams;
+    long n_out;
+    long pos0, step;      // output schedule on the L-times upsampled grid of the (virtual) decimated stream
+    int L, D;
+    long n_first;         // raw index of decimated sample 0 of this call
+    int H;                // history depth in samples, multiple of 32
+    const float *table;   // device: n_rows rows of row_len floats (bank_table)
+    int row_len, n_rows;
+    int rows_per_phase;   // 1: one alignment per call (D % 4 == 0), 4: row = ph*4 + alignment
+    // filled by launch_bank
+    int n_groups, n_seg;
+};
+void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r, int L, double scale, int e_only,
+                std::vector<float> &rows, int *row_len, int *n_rows, int *Tc);
+size_t bank_smem_bytes(int n_rows, int row_len);
+int bank_max_live();
+int launch_bank(const BankParams &p, cudaStream_t st);
+
 // ---- small utilities (util_kernels.cu) -----------------------------------------------------------
 // hist_new[s][0..H) <- last H samples of (hist_old ++ cur[0..n)) for every stream row; elem = bytes per sample
 int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long pitch, long n, int H, int elem, int n_streams,

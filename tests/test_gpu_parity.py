@@ -125,10 +125,11 @@ def _chain(cfg, flags=0, S=None):
 
 
 @pytest.mark.parametrize("name", ["cfg1_small", "cfg2_small", "cfg3_small", "cfg4_small", "cfg5_small"])
-@pytest.mark.parametrize("flags", [0, 2, 1])
+@pytest.mark.parametrize("flags", [0, 8, 8 + 2, 1])
 def test_chain_vs_golden(gpu_lib, name, flags):
     """small cases of every BASELINE config against the committed reference outputs (tests/golden/chain.npz);
-    flags: 0 = default plan (fused where possible), 2 = NO_FUSE (FFT blkconv + separate stages), 1 = EXACT"""
+    flags: 0 = default plan (one fused polyphase bank where the schedules are integral), 8 = NO_BANK (staged plan,
+    blkconv folded into the decimator), 8+2 = NO_BANK|NO_FUSE (FFT blkconv + separate stages), 1 = EXACT"""
     cfg = F.CONFIGS[name]
     iq = F.make_input(cfg)
     ch = _chain(cfg, flags)
@@ -248,14 +249,14 @@ def test_chain_tensor_path_vs_oracle(gpu_lib, oracle_lib, base, S, N):
     iq[1, :100] = -32768
     iq[2, 100:300, 0] = -1
     ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=4)
-    ch = _chain(cfg)
+    ch = _chain(cfg, flags=8)
     assert "toeplitz_i8_tcgen05" in ch.plan, ch.plan
     got = ch.process(iq)
     assert got.shape == ref.shape, (got.shape, ref.shape)
     nrms, peak = F.err_metrics(got, ref)
     assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
     # and against the CUDA-core plan of the same chain
-    alt = _chain(cfg, flags=4).process(iq)
+    alt = _chain(cfg, flags=8 + 4).process(iq)
     nrms, peak = F.err_metrics(got, alt)
     assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
 
@@ -263,8 +264,8 @@ def test_chain_tensor_path_vs_oracle(gpu_lib, oracle_lib, base, S, N):
 def test_chain_tensor_path_chunk_invariance(gpu_lib):
     cfg = dict(F.CONFIGS["cfg5_small"], S=9, N=40000)
     iq = F.make_input(cfg)
-    one = _chain(cfg).process(iq)
-    ch = _chain(cfg)
+    one = _chain(cfg, flags=8).process(iq)
+    ch = _chain(cfg, flags=8)
     assert "toeplitz_i8_tcgen05" in ch.plan
     parts, off = [], 0
     for n in (1, 7, 1000, 4096, 12345, 3, 10 ** 9):
@@ -277,3 +278,68 @@ def test_chain_tensor_path_chunk_invariance(gpu_lib):
     assert many.shape == one.shape
     nrms, peak = F.err_metrics(many, one)
     assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
+
+
+# ---- K3: the whole chain as one fused polyphase bank (TMA-staged int16 rows, one stream per lane) ------
+
+@pytest.mark.parametrize("base,S,N", [("cfg5_small", 70, 70001), ("cfg5_small", 1, 30011), ("cfg3_small", 37, 200001),
+                                      ("cfg5_small", 33, 4099)])
+def test_chain_bank_path_vs_oracle(gpu_lib, oracle_lib, base, S, N):
+    from oracle import oracle as O
+    cfg = dict(F.CONFIGS[base], S=S, N=N)
+    iq = F.make_input(cfg)
+    iq[0, :100] = 32767
+    iq[-1, :100] = -32768
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=4)
+    ch = _chain(cfg)
+    assert ch.plan.startswith("bank_fused"), ch.plan
+    got = ch.process(iq)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
+    for s in range(S):                      # every stream on its own: a swapped or stale row must not hide in the mean
+        nrms, peak = F.err_metrics(got[s], ref[s])
+        assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (s, nrms, peak)
+    alt = _chain(cfg, flags=8).process(iq)  # and against the staged plan of the same chain
+    nrms, peak = F.err_metrics(got, alt)
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
+
+
+@pytest.mark.parametrize("base,S", [("cfg5_small", 35), ("cfg3_small", 3)])
+def test_chain_bank_path_chunk_invariance(gpu_lib, base, S):
+    """ragged call sizes: history rows, held-over outputs and changing sample alignment (n_first mod 4)"""
+    cfg = dict(F.CONFIGS[base], S=S, N=60013)
+    iq = F.make_input(cfg)
+    one = _chain(cfg).process(iq)
+    ch = _chain(cfg)
+    assert ch.plan.startswith("bank_fused")
+    parts, off = [], 0
+    for n in (1, 7, 1000, 4096, 12345, 3, 2, 5001, 10 ** 9):
+        n = min(n, cfg["N"] - off)
+        if n <= 0:
+            break
+        parts.append(ch.process(iq[:, off:off + n]))
+        off += n
+    many = np.concatenate(parts, axis=1)
+    assert many.shape == one.shape
+    nrms, peak = F.err_metrics(many, one)
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
+
+
+def test_chain_bank_unaligned_device_rows(gpu_lib):
+    """caller rows that TMA cannot address (odd pitch, 4-byte aligned base) are realigned on the device"""
+    import torch
+    cfg = dict(F.CONFIGS["cfg5_small"], S=6, N=30001)
+    iq = F.make_input(cfg)
+    want = _chain(cfg).process(iq)
+    ch = _chain(cfg)
+    pitch = cfg["N"] + 3
+    buf = torch.zeros(cfg["S"] * pitch * 2 + 2, dtype=torch.int16, device="cuda")
+    view = buf[2:].view(cfg["S"], pitch, 2)
+    view[:, :cfg["N"]] = torch.from_numpy(iq).cuda()
+    cap = ch.max_out(cfg["N"])
+    d_out = torch.zeros((cfg["S"], cap, 2), dtype=torch.float32, device="cuda")
+    n = ch.process_dev(buf.data_ptr() + 4, cfg["N"], pitch, d_out.data_ptr(), cap, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    got = d_out.cpu().numpy()[:, :n].view(np.complex64)[..., 0]
+    assert np.array_equal(got, want)
