@@ -168,7 +168,7 @@ def run_reference(args, cfg, rank, world):
     v = S * cfg["N"] * args.steps / dt / 1e6
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(cfg, args.gpus),
         "cpu_baseline": {"value": v, "unit": METRIC, "cores": T, "kind": lib.sfeo_kind().decode(),
@@ -180,11 +180,13 @@ def run_reference(args, cfg, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(cfg, n_gpus):
-    return {"workload": "cfg5: 1024 int16 IQ streams x 2^20 samples, blkconv(255 taps, FFT 4096) -> decimate(128 taps, /8) "
+def workload_config(cfg, n_gpus, streams_per_gpu=None, scaling="weak"):
+    spg = streams_per_gpu if streams_per_gpu is not None else cfg["S"]
+    return {"workload": "cfg5: 1024 int16 IQ streams x 2^20 samples per GPU, blkconv(255 taps, FFT 4096) -> decimate(128 taps, /8) "
                         "-> resample(512 taps, L=24, rate 625/24)",
-            "streams_total": cfg["S"], "samples_per_stream": cfg["N"], "streams_per_gpu": cfg["S"] // n_gpus,
-            "partition": f"streams over {n_gpus} GPU(s), no collective", "l2": "inputs larger than L2 (no flush needed)"}
+            "streams_total": spg * n_gpus, "samples_per_stream": cfg["N"], "streams_per_gpu": spg,
+            "partition": f"independent streams over {n_gpus} GPU(s) ({scaling}), no collective",
+            "l2": "inputs larger than L2 (no flush needed)"}
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -199,6 +201,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--flags", type=int, default=0, help="SFE_FLAG_* for the chain (debug)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every GPU runs the full 1024-stream shard (box = N x 1024 streams); "
+                         "strong: the 1024 streams are split over the N GPUs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -225,8 +230,11 @@ def main():
     lib = simplefe_b200.lib()
     simplefe_b200._lib.check(lib.sfe_set_device(local_rank), "sfe_set_device")
 
-    S_total, N = cfg["S"], cfg["N"]
-    S = S_total // n_ranks                      # strong scaling: the 1024 streams are partitioned
+    N = cfg["N"]
+    # the path shards by stream with no data-path collective.  weak (default): each GPU carries the
+    # full single-GPU shard of cfg["S"] streams; strong: cfg["S"] streams are split over the ranks.
+    S = cfg["S"] if args.scaling == "weak" else cfg["S"] // n_ranks
+    S_total = S * n_ranks
     dev = torch.device("cuda", local_rank)
 
     # synthetic int16 IQ, generated on the device (N(0, 0.25^2) clipped, round(x * 32767)); rank-distinct seed
@@ -345,8 +353,8 @@ def main():
 
     line = {
         "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": n_ranks, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": dict(workload_config(cfg, n_ranks), plan=ch.plan, outputs_per_stream=n_out),
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": dict(workload_config(cfg, n_ranks, S, args.scaling), plan=ch.plan, outputs_per_stream=n_out),
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)
