@@ -149,6 +149,28 @@ int sfe_chain_profile_enable(sfe_chain *c, int on);
    (synchronises on the recorded events); *n_samples = launches averaged */
 int sfe_chain_profile_read(sfe_chain *c, int op, float *mean_ms, int *n_samples);
 
+/* ---- (3) ring_buffer<T>: libdsp/ringbuf.h:37-142 (same body in gr-simplefe/lib/ringbuf.h:40-145) ------ */
+/* Byte-oriented twin of the reference template; include/libdsp/ringbuf.h forwards ring_buffer<T> to
+   it with elem_bytes = sizeof(T).  Storage is page-locked host memory.  No internal locking: callers
+   serialise, as the reference's users do (bpsk.cxx:108-116,132-170). */
+typedef struct sfe_ring sfe_ring;
+typedef int (*sfe_ring_conv_fn)(void *dst, void *src, int src_len);   /* returns BYTES written to dst */
+typedef int (*sfe_ring_len_fn)(int dst_len);                           /* elements needed for dst_len */
+sfe_ring *sfe_ring_create(int elem_bytes, int capacity);   /* ring_buffer() / ring_buffer(int)  :40-53;
+                                                              capacity 0 = no storage yet             */
+int sfe_ring_alloc(sfe_ring *r, int capacity);             /* alloc_buffer  :60-69                    */
+void sfe_ring_destroy(sfe_ring *r);                        /* ~ring_buffer  :54-57                    */
+int sfe_ring_space(sfe_ring *r);                           /* get_space     :71-74                    */
+int sfe_ring_count(sfe_ring *r);                           /* get_count     :75-78                    */
+int sfe_ring_write(sfe_ring *r, const void *data, int len);/* write         :80-101: len or 0         */
+int sfe_ring_read(sfe_ring *r, void *dst, unsigned dst_len, sfe_ring_conv_fn conv,
+                  sfe_ring_len_fn calc_src_len);           /* read          :106-134: elements or 0   */
+/* additive: move the next n elements to device memory with <= 2 cudaMemcpyAsync on `stream` and
+   return at once (n, or 0 when fewer are buffered); their space becomes writable again when the
+   copy has completed.  This is the producer/consumer decoupling of the reference with a copy
+   engine as the consumer. */
+int sfe_ring_read_dev(sfe_ring *r, void *d_dst, int n, void *stream);
+
 /* ---- sample format helpers (device wire formats) ---------------------- */
 /* float -> 10-bit DAC words, 4 samples -> 5 bytes: examples/bpsk/bpsk.cxx:76-101,
    gr-simplefe/lib/sink_c_impl.cc:118-144.  n must be a multiple of 4; device pointers. */

@@ -22,6 +22,9 @@ class ChainDesc(C.Structure):
                 ("bc_ntaps", C.c_int), ("bc_fft", C.c_int), ("a", StageDesc), ("b", StageDesc), ("flags", C.c_int)]
 
 
+RING_CONV = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int)
+RING_LEN = C.CFUNCTYPE(C.c_int, C.c_int)
+
 # every symbol include/sfe_gpu.h declares: (restype, argtypes)
 _f32p = C.POINTER(C.c_float)
 _vp, _ci, _cl, _cf = C.c_void_p, C.c_int, C.c_long, C.c_float
@@ -60,6 +63,14 @@ SYMBOLS = {
     "sfe_chain_profile_enable": (_ci, [_vp, _ci]),
     "sfe_chain_profile_read": (_ci, [_vp, _ci, C.POINTER(C.c_float), C.POINTER(_ci)]),
     "sfe_pack_dac10_dev": (_ci, [_vp, _cl, _vp, _vp]),
+    "sfe_ring_create": (_vp, [_ci, _ci]),
+    "sfe_ring_alloc": (_ci, [_vp, _ci]),
+    "sfe_ring_destroy": (None, [_vp]),
+    "sfe_ring_space": (_ci, [_vp]),
+    "sfe_ring_count": (_ci, [_vp]),
+    "sfe_ring_write": (_ci, [_vp, _vp, _ci]),
+    "sfe_ring_read": (_ci, [_vp, _vp, C.c_uint, RING_CONV, RING_LEN]),
+    "sfe_ring_read_dev": (_ci, [_vp, _vp, _ci, _vp]),
 }
 
 _lib = None
