@@ -233,7 +233,13 @@ def main():
     N = cfg["N"]
     # the path shards by stream with no data-path collective.  weak (default): each GPU carries the
     # full single-GPU shard of cfg["S"] streams; strong: cfg["S"] streams are split over the ranks.
-    S = cfg["S"] if args.scaling == "weak" else cfg["S"] // n_ranks
+    from simplefe_b200.shard import shard_range
+    if args.scaling == "weak":
+        S = cfg["S"]
+    else:
+        lo, hi = shard_range(cfg["S"], rank, n_ranks)
+        S = hi - lo
+        assert cfg["S"] % n_ranks == 0, "strong scaling bench expects streams divisible by the GPU count"
     S_total = S * n_ranks
     dev = torch.device("cuda", local_rank)
 
