@@ -192,19 +192,20 @@ void plan_call(sfe_chain *c, long n_in)
             op.n_first = 0;
             op.bad_sched = false;
             if (op.has_pre) {
-                walk_batch(op.pre_ws, op.pre_up, op.pre_blk, op.pre_rate, n, op.pre_sched);
-                na = (long)op.pre_sched.e.size();
+                walk_batch(op.pre_ws, op.pre_up, op.pre_blk, op.pre_rate, n, op.pre_sched, false);
+                na = (long)op.pre_sched.count;
                 if (na > 0) {
                     op.bad_sched = !op.pre_sched.uniform || op.pre_sched.step != (int64_t)op.D * op.pre_up;
                     op.n_first = op.pre_sched.pos0 >= 0 ? op.pre_sched.pos0 / op.pre_up : -1;
                 }
             }
-            walk_batch(op.ws, op.up, op.blk, op.rate, na, op.sched);
-            op.n_out = (long)op.sched.e.size();
+            walk_batch(op.ws, op.up, op.blk, op.rate, na, op.sched, false);
+            op.n_out = (long)op.sched.count;
             if (op.n_out > 0 && !op.sched.uniform) op.bad_sched = true;
         } else {
-            walk_batch(op.ws, op.up, op.blk, op.rate, n, op.sched);
-            op.n_out = (long)op.sched.e.size();
+            // the closed-form kernels only need the summary; the generic kernel wants every (pos, mu)
+            walk_batch(op.ws, op.up, op.blk, op.rate, n, op.sched, op.kind == OP_POLY);
+            op.n_out = (long)op.sched.count;
         }
         n = op.n_out;
     }

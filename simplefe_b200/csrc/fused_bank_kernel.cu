@@ -31,12 +31,10 @@ namespace sfe {
 
 namespace {
 
-constexpr int BK_WARPS = 8;          // work items per CTA
-constexpr int BK_NST = 2;            // ring stages per warp
-constexpr int BK_BPS = 2;            // TMA boxes per stage
 constexpr int BOX_SAMPLES = 32, BOX_ROWS = 32;
-constexpr int BOX_BYTES = BOX_SAMPLES * BOX_ROWS * 4;
-constexpr int STAGE_BYTES = BK_BPS * BOX_BYTES;
+constexpr int BOX_BYTES = BOX_SAMPLES * BOX_ROWS * 4;   // one TMA box = one ring slot = 8 chunks of 4 samples per lane
+constexpr int SLOT_BOXES = 2;         // boxes (time blocks of 128 B per row) fetched by one TMA instruction
+constexpr int SLOT_BYTES = SLOT_BOXES * BOX_BYTES;
 constexpr int A_MAX = 4;             // live outputs per lane
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -62,18 +60,143 @@ __device__ __forceinline__ void tma_box(uint32_t dst, const CUtensorMap *map, in
                  ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar) : "memory");
 }
 
-// the two int16 halves of a word as int32: PRMT with sign replication (selector nibble bit 3), one ALU op each
-__device__ __forceinline__ int sext_lo(uint32_t w)
+__device__ __forceinline__ void tma_box3(uint32_t dst, const CUtensorMap *map, int tb, int y, uint32_t bar)
 {
-    int r;
-    asm("prmt.b32 %0, %1, %1, 0x9910;" : "=r"(r) : "r"(w));
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(map), "r"(0), "r"(tb), "r"(y), "r"(bar) : "memory");
+}
+
+// ---- packed single precision (sm_100: FFMA2 / FADD2 work on an aligned register pair) -------------------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
     return r;
 }
-__device__ __forceinline__ int sext_hi(uint32_t w)
+__device__ __forceinline__ float2 unpack2(f32x2 v)
+{
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 fadd2(f32x2 a, f32x2 b)
+{
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// shared-memory loads by 32-bit address.  volatile: the ring slots are rewritten by the TMA (async proxy) behind
+// the compiler's back, so these loads must neither be merged across laps nor moved over the mbarrier wait.
+__device__ __forceinline__ uint4 lds_u4(uint32_t addr)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+template <int OFF>
+__device__ __forceinline__ void lds_taps(uint32_t addr, f32x2 &t01, f32x2 &t23)
+{
+    asm volatile("ld.shared.v2.u64 {%0, %1}, [%2+%3];" : "=l"(t01), "=l"(t23) : "r"(addr), "n"(OFF));
+}
+
+// ---- int16 I/Q -> float, four complex samples (one 128-bit word) into (even, odd) pairs ------------------
+// CONV 0: PRMT sign extension + I2FP (ALU pipe);  1: I2F.S16 on the packed halves (XU pipe);
+// 2: I through the XU, Q through the ALU;  3: exponent trick, exact: bits 0x4B40_0000 | (s ^ 0x8000) are the float
+//    12582912 + 32768 + s, one packed FADD2 removes the offset for two values.
+__device__ __forceinline__ float cvt_lo_alu(uint32_t w)
+{
+    int r;
+    asm("prmt.b32 %0, %1, %1, 0x9910;" : "=r"(r) : "r"(w));   // bytes (b0, b1, sign, sign)
+    return (float)r;
+}
+__device__ __forceinline__ float cvt_hi_alu(uint32_t w)
 {
     int r;
     asm("prmt.b32 %0, %1, %1, 0xBB32;" : "=r"(r) : "r"(w));
-    return r;
+    return (float)r;
+}
+__device__ __forceinline__ float cvt_lo_xu(uint32_t w)
+{
+    float f;
+    asm("{\n .reg .b16 l, h;\n mov.b32 {l, h}, %1;\n cvt.rn.f32.s16 %0, l;\n}\n" : "=f"(f) : "r"(w));
+    return f;
+}
+__device__ __forceinline__ float cvt_hi_xu(uint32_t w)
+{
+    float f;
+    asm("{\n .reg .b16 l, h;\n mov.b32 {l, h}, %1;\n cvt.rn.f32.s16 %0, h;\n}\n" : "=f"(f) : "r"(w));
+    return f;
+}
+template <int CONV>
+__device__ __forceinline__ void convert4(const uint4 &w, f32x2 &i01, f32x2 &i23, f32x2 &q01, f32x2 &q23)
+{
+    if (CONV == 3) {
+        const uint32_t K = 0x4B400000u;
+        const f32x2 off = pack2(-12615680.0f, -12615680.0f);
+        const uint32_t a = w.x ^ 0x80008000u, b = w.y ^ 0x80008000u, c = w.z ^ 0x80008000u, d = w.w ^ 0x80008000u;
+        i01 = fadd2(pack2(__uint_as_float(__byte_perm(a, K, 0x7610)), __uint_as_float(__byte_perm(b, K, 0x7610))), off);
+        q01 = fadd2(pack2(__uint_as_float(__byte_perm(a, K, 0x7632)), __uint_as_float(__byte_perm(b, K, 0x7632))), off);
+        i23 = fadd2(pack2(__uint_as_float(__byte_perm(c, K, 0x7610)), __uint_as_float(__byte_perm(d, K, 0x7610))), off);
+        q23 = fadd2(pack2(__uint_as_float(__byte_perm(c, K, 0x7632)), __uint_as_float(__byte_perm(d, K, 0x7632))), off);
+    } else {
+        const bool ixu = CONV == 1 || CONV == 2, qxu = CONV == 1;
+        i01 = pack2(ixu ? cvt_lo_xu(w.x) : cvt_lo_alu(w.x), ixu ? cvt_lo_xu(w.y) : cvt_lo_alu(w.y));
+        i23 = pack2(ixu ? cvt_lo_xu(w.z) : cvt_lo_alu(w.z), ixu ? cvt_lo_xu(w.w) : cvt_lo_alu(w.w));
+        q01 = pack2(qxu ? cvt_hi_xu(w.x) : cvt_hi_alu(w.x), qxu ? cvt_hi_xu(w.y) : cvt_hi_alu(w.y));
+        q23 = pack2(qxu ? cvt_hi_xu(w.z) : cvt_hi_alu(w.z), qxu ? cvt_hi_xu(w.w) : cvt_hi_alu(w.w));
+    }
+}
+
+// one chunk (4 samples of this lane's stream) into NA live windows.  Accumulators hold (even, odd) partial sums:
+// the pair of consecutive samples meets the pair of consecutive taps in one FFMA2.
+template <int NA, int CONV, int TOFF>
+__device__ __forceinline__ void chunk(uint32_t addr, f32x2 (&accI)[A_MAX], f32x2 (&accQ)[A_MAX], const uint32_t (&tp)[A_MAX])
+{
+    const uint4 w = lds_u4(addr);
+    f32x2 i01, i23, q01, q23;
+    convert4<CONV>(w, i01, i23, q01, q23);
+#pragma unroll
+    for (int j = 0; j < NA; j++) {
+        f32x2 t01, t23;
+        lds_taps<TOFF>(tp[j], t01, t23);
+        accI[j] = ffma2(i01, t01, accI[j]);
+        accQ[j] = ffma2(q01, t01, accQ[j]);
+        accI[j] = ffma2(i23, t23, accI[j]);
+        accQ[j] = ffma2(q23, t23, accQ[j]);
+    }
+}
+
+// chunks [c0, c1) of the current box (0 <= c0 < c1 <= 8).  ax = slot base | lane row | (lane & 7) << 4: the 16-byte
+// slot of chunk c inside this lane's 128-byte row is c ^ (lane & 7) (SWIZZLE_128B), i.e. address ax ^ (c << 4).
+template <int NA, int CONV>
+__device__ __forceinline__ void run_chunks(uint32_t ax, int c0, int c1, f32x2 (&accI)[A_MAX], f32x2 (&accQ)[A_MAX], uint32_t (&tp)[A_MAX])
+{
+    if (c0 == 0 && c1 == 8) {            // a whole box without events: the common case, fully unrolled
+        chunk<NA, CONV, 0>(ax, accI, accQ, tp);
+        chunk<NA, CONV, 16>(ax ^ 0x10u, accI, accQ, tp);
+        chunk<NA, CONV, 32>(ax ^ 0x20u, accI, accQ, tp);
+        chunk<NA, CONV, 48>(ax ^ 0x30u, accI, accQ, tp);
+        chunk<NA, CONV, 64>(ax ^ 0x40u, accI, accQ, tp);
+        chunk<NA, CONV, 80>(ax ^ 0x50u, accI, accQ, tp);
+        chunk<NA, CONV, 96>(ax ^ 0x60u, accI, accQ, tp);
+        chunk<NA, CONV, 112>(ax ^ 0x70u, accI, accQ, tp);
+#pragma unroll
+        for (int j = 0; j < NA; j++) tp[j] += 128;
+    } else {
+        for (int c = c0; c < c1; c++) {
+            chunk<NA, CONV, 0>(ax ^ ((uint32_t)c << 4), accI, accQ, tp);
+#pragma unroll
+            for (int j = 0; j < NA; j++) tp[j] += 16;
+        }
+    }
 }
 
 struct OutInfo {
@@ -81,140 +204,155 @@ struct OutInfo {
     int row;   // row of the bank table
 };
 
-__device__ __forceinline__ OutInfo out_info(const BankParams &p, long k)
+// output at decimated index M, phase ph
+__device__ __forceinline__ OutInfo out_info(const BankParams &p, long M, int ph)
 {
-    const long pos = p.pos0 + k * p.step;
-    long M = pos / p.L;
-    int ph = (int)(pos - M * p.L);
-    if (ph < 0) { ph += p.L; M -= 1; }                    // floor division: pos = -1 is a held-over output
     const long rh = p.n_first + (long)p.D * M + p.H;      // newest sample, counted from sample -H
     OutInfo o;
     o.E = (int)(rh >> 2);
     o.row = p.rows_per_phase == 4 ? ph * 4 + (int)(rh & 3) : ph;
     return o;
 }
-
-// NA live windows over chunks [c0, c1) of the current ring stage (chunk = 4 samples = one 128-bit word per lane)
-template <int NA>
-__device__ __forceinline__ void run_chunks(const uint8_t *sp, int c0, int c1, uint32_t lane_x, float2 (&acc)[A_MAX],
-                                           const float4 *(&tp)[A_MAX])
+__device__ __forceinline__ void split_pos(const BankParams &p, long k, long &M, int &ph)
 {
-#pragma unroll 2
-    for (int c = c0; c < c1; c++) {
-        // box (c >> 3) of the stage, 16-byte slot (c & 7) ^ (row & 7) of this lane's 128-byte row (SWIZZLE_128B)
-        const uint4 w = *reinterpret_cast<const uint4 *>(sp + (c >> 3) * BOX_BYTES + ((((uint32_t)c & 7u) ^ lane_x) << 4));
-        float xi[4], xq[4];
-        xi[0] = (float)sext_lo(w.x); xq[0] = (float)sext_hi(w.x);
-        xi[1] = (float)sext_lo(w.y); xq[1] = (float)sext_hi(w.y);
-        xi[2] = (float)sext_lo(w.z); xq[2] = (float)sext_hi(w.z);
-        xi[3] = (float)sext_lo(w.w); xq[3] = (float)sext_hi(w.w);
-#pragma unroll
-        for (int j = 0; j < NA; j++) {
-            const float4 t = *tp[j];
-            tp[j]++;
-            acc[j].x = fmaf(t.x, xi[0], acc[j].x); acc[j].y = fmaf(t.x, xq[0], acc[j].y);
-            acc[j].x = fmaf(t.y, xi[1], acc[j].x); acc[j].y = fmaf(t.y, xq[1], acc[j].y);
-            acc[j].x = fmaf(t.z, xi[2], acc[j].x); acc[j].y = fmaf(t.z, xq[2], acc[j].y);
-            acc[j].x = fmaf(t.w, xi[3], acc[j].x); acc[j].y = fmaf(t.w, xq[3], acc[j].y);
-        }
-    }
+    const long pos = p.pos0 + k * p.step;
+    M = pos / p.L;
+    ph = (int)(pos - M * p.L);
+    if (ph < 0) { ph += p.L; M -= 1; }                    // floor division: pos = -1 is a held-over output
 }
 
-__global__ void __launch_bounds__(BK_WARPS * 32, 1)
-fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_constant__ CUtensorMap map_hist, const BankParams p)
+template <int WARPS, int NST, int CONV>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_constant__ CUtensorMap map_hist,
+                  const __grid_constant__ CUtensorMap map_cur3, const __grid_constant__ CUtensorMap map_hist3, const BankParams p)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bars[BK_WARPS * BK_NST];
+    __shared__ __align__(8) uint64_t bars[WARPS * NST];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *sbase = smem + ((1024u - (smem_u32(smem) & 1023u)) & 1023u);   // SWIZZLE_128B boxes: 1024 B alignment
-    uint8_t *ring = sbase + (size_t)warp * BK_NST * STAGE_BYTES;
-    float *table = reinterpret_cast<float *>(sbase + (size_t)BK_WARPS * BK_NST * STAGE_BYTES);
+    float *table = reinterpret_cast<float *>(sbase + (size_t)WARPS * NST * SLOT_BYTES);
+    const uint32_t ring_a = smem_u32(sbase) + (uint32_t)warp * NST * SLOT_BYTES;
+    const uint32_t table_a = smem_u32(table);
 
     // ---- one-time: bank table -> shared memory, barriers ------------------------------------------------
     {
         const int n16 = p.n_rows * p.row_len / 4;
         const float4 *src = reinterpret_cast<const float4 *>(p.table);
         float4 *dst = reinterpret_cast<float4 *>(table);
-        for (int i = threadIdx.x; i < n16; i += BK_WARPS * 32) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < n16; i += WARPS * 32) dst[i] = __ldg(src + i);
     }
     if (lane == 0) {
-        for (int s = 0; s < BK_NST; s++) mbar_init(smem_u32(&bars[warp * BK_NST + s]), 1);
+        for (int s = 0; s < NST; s++) mbar_init(smem_u32(&bars[warp * NST + s]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     __syncthreads();
 
     // ---- this warp's work item ---------------------------------------------------------------------------
-    const long item = (long)blockIdx.x * BK_WARPS + warp;
+    const long item = (long)blockIdx.x * WARPS + warp;
     if (item >= (long)p.n_groups * p.n_seg) return;
     const int g = (int)(item % p.n_groups), seg = (int)(item / p.n_groups);
     const long k_lo = p.n_out * seg / p.n_seg, k_hi = p.n_out * (seg + 1) / p.n_seg;
     if (k_lo >= k_hi) return;
     const int NC = p.row_len >> 2;
+    const int row_bytes = p.row_len * 4;
 
-    const OutInfo first = out_info(p, k_lo), last = out_info(p, k_hi - 1);
+    long M_next;
+    int ph_next;
+    split_pos(p, k_lo, M_next, ph_next);
+    const OutInfo first = out_info(p, M_next, ph_next);
+    OutInfo last;
+    {
+        long Ml;
+        int phl;
+        split_pos(p, k_hi - 1, Ml, phl);
+        last = out_info(p, Ml, phl);
+    }
     const int q_begin = first.E - NC + 1, q_end = last.E;          // chunks this item reads (inclusive)
-    const int box0 = q_begin >> 3, box1 = q_end >> 3;              // 8 chunks per box
-    const int n_batches = (box1 - box0) / BK_BPS + 1;
+    const int box0 = q_begin >> 3;                                 // 8 chunks per box
+    const int n_boxes = (q_end >> 3) - box0 + 1;
+    const int slot0 = box0 >> 1;                                   // slots pair boxes (2a, 2a+1) of the absolute box grid
+    const int n_slots = (q_end >> 4) - slot0 + 1;
     const int hist_boxes = p.H >> 5;
-    const uint32_t bar0 = smem_u32(&bars[warp * BK_NST]);
-    const uint32_t ring_a = smem_u32(ring);
+    const int full_tb = (int)(p.in.n >> 5);                        // whole 128-byte time blocks of the current rows
+    const uint32_t bar0 = smem_u32(&bars[warp * NST]);
 
-    auto issue = [&](int batch) {                                  // lane 0 only
-        const int st = batch % BK_NST;
-        const uint32_t bar = bar0 + 8 * st;
-        mbar_expect_tx(bar, STAGE_BYTES);
+    // A slot whose two boxes are whole blocks of the same buffer comes in as ONE 3-D box (32 samples, 2 blocks, 32 rows):
+    // each row contributes 256 contiguous bytes, which is what lets HBM run at full rate (128-byte pieces cap it near
+    // 5.3 TB/s, tests/probes/tma_box_bw.cu).  Edge slots (history/current seam, ragged end) use two 2-D boxes, whose
+    // out-of-range samples the TMA zero-fills.
+    auto slot_3d = [&](int a) -> bool {
+        const int b0 = 2 * a, b1 = 2 * a + 1;
+        return b1 < hist_boxes || (b0 >= hist_boxes && b1 - hist_boxes < full_tb);
+    };
+    auto issue = [&](int a, int rs) {                              // lane 0 only; a = absolute slot, rs = ring slot
+        const uint32_t bar = bar0 + 8 * rs;
+        mbar_expect_tx(bar, SLOT_BYTES);
+        const uint32_t dst = ring_a + rs * SLOT_BYTES;
+        const int b0 = 2 * a;                                      // box b holds samples [32 b - H, 32 b - H + 32)
+        if (slot_3d(a)) {
+            if (b0 < hist_boxes) tma_box3(dst, &map_hist3, b0, g * BOX_ROWS, bar);
+            else tma_box3(dst, &map_cur3, b0 - hist_boxes, g * BOX_ROWS, bar);
+        } else {
 #pragma unroll
-        for (int b = 0; b < BK_BPS; b++) {
-            const int box = box0 + batch * BK_BPS + b;             // samples [32 box - H, 32 box - H + 32)
-            const uint32_t dst = ring_a + st * STAGE_BYTES + b * BOX_BYTES;
-            if (box < hist_boxes) tma_box(dst, &map_hist, box * BOX_SAMPLES, g * BOX_ROWS, bar);
-            else tma_box(dst, &map_cur, (box - hist_boxes) * BOX_SAMPLES, g * BOX_ROWS, bar);
+            for (int t = 0; t < SLOT_BOXES; t++) {
+                const int box = b0 + t;
+                if (box < hist_boxes) tma_box(dst + t * BOX_BYTES, &map_hist, box * BOX_SAMPLES, g * BOX_ROWS, bar);
+                else tma_box(dst + t * BOX_BYTES, &map_cur, (box - hist_boxes) * BOX_SAMPLES, g * BOX_ROWS, bar);
+            }
         }
     };
     if (lane == 0)
-        for (int b = 0; b < BK_NST && b < n_batches; b++) issue(b);
+        for (int b = 0; b < NST && b < n_slots; b++) issue(slot0 + b, b);
 
     // ---- live outputs (slot 0 finishes first) ---------------------------------------------------------
-    float2 acc[A_MAX];
-    const float4 *tp[A_MAX];
+    f32x2 accI[A_MAX], accQ[A_MAX];
+    uint32_t tp[A_MAX];
     int Es[A_MAX];
 #pragma unroll
     for (int j = 0; j < A_MAX; j++) {
-        acc[j] = make_float2(0.f, 0.f);
-        tp[j] = reinterpret_cast<const float4 *>(table);
+        accI[j] = accQ[j] = 0ull;
+        tp[j] = table_a;
         Es[j] = 0x3fffffff;
     }
     int nact = 0;
     long k_next = k_lo, k_head = k_lo;
     OutInfo nxt = first;
     int S_next = q_begin;
+    const int sM = (int)(p.step / p.L), sP = (int)(p.step % p.L);   // schedule stepping without division
     const int s_row = g * BOX_ROWS + lane;
     float2 *orow = p.out + (long)s_row * p.out_pitch;
     const bool s_ok = s_row < p.n_streams;
-    const uint32_t lane_off = (uint32_t)lane * 128u, lane_x = (uint32_t)(lane & 7);
 
-    for (int batch = 0; batch < n_batches; batch++) {
-        const int st = batch % BK_NST;
-        mbar_wait(bar0 + 8 * st, (uint32_t)((batch / BK_NST) & 1));
-        const int qb = (box0 + batch * BK_BPS) << 3;               // first chunk of this stage
-        const uint8_t *sp = ring + st * STAGE_BYTES + lane_off;
+    int slot = 0;
+    uint32_t phase = 0;
+    for (int bi = 0; bi < n_boxes; bi++) {
+        const int B = box0 + bi, a = B >> 1, tb = B & 1;
+        if (bi == 0 || tb == 0) mbar_wait(bar0 + 8 * slot, phase);   // first box of a slot
+        const int qb = B << 3;                                       // first chunk of this box
+        // this lane's 128-byte line of the box, with the SWIZZLE_128B term (line index & 7) << 4 in bits 4-6:
+        // chunk c sits at ax ^ (c << 4).  3-D slot: lines (2 lane + tb); 2-D boxes: box tb, line lane.
+        const uint32_t line = slot_3d(a) ? (uint32_t)(2 * lane + tb) : (uint32_t)(tb * BOX_ROWS + lane);
+        const uint32_t ax = ring_a + slot * SLOT_BYTES + line * 128u + ((line & 7u) << 4);
         int q = qb > q_begin ? qb : q_begin;
-        const int q_stop = (qb + 8 * BK_BPS) <= q_end + 1 ? (qb + 8 * BK_BPS) : q_end + 1;
+        const int q_stop = (qb + 8) <= q_end + 1 ? (qb + 8) : q_end + 1;
         while (q < q_stop) {
             if (q == S_next) {                                     // a window opens (at most one per chunk)
 #pragma unroll
                 for (int j = 0; j < A_MAX; j++)
                     if (j == nact) {
-                        acc[j] = make_float2(0.f, 0.f);
-                        tp[j] = reinterpret_cast<const float4 *>(table + (size_t)nxt.row * p.row_len);
+                        accI[j] = accQ[j] = 0ull;
+                        tp[j] = table_a + (uint32_t)(nxt.row * row_bytes);
                         Es[j] = nxt.E;
                     }
                 nact++;
                 k_next++;
                 if (k_next < k_hi) {
-                    nxt = out_info(p, k_next);
+                    ph_next += sP;
+                    M_next += sM;
+                    if (ph_next >= p.L) { ph_next -= p.L; M_next += 1; }
+                    nxt = out_info(p, M_next, ph_next);
                     S_next = nxt.E - NC + 1;
                 } else {
                     S_next = 0x3fffffff;
@@ -224,19 +362,21 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
             int run_end = q_stop < S_next ? q_stop : S_next;
             if (Es[0] + 1 < run_end) run_end = Es[0] + 1;
             switch (nact) {
-                case 1: run_chunks<1>(sp, q - qb, run_end - qb, lane_x, acc, tp); break;
-                case 2: run_chunks<2>(sp, q - qb, run_end - qb, lane_x, acc, tp); break;
-                case 3: run_chunks<3>(sp, q - qb, run_end - qb, lane_x, acc, tp); break;
-                case 4: run_chunks<4>(sp, q - qb, run_end - qb, lane_x, acc, tp); break;
+                case 1: run_chunks<1, CONV>(ax, q - qb, run_end - qb, accI, accQ, tp); break;
+                case 2: run_chunks<2, CONV>(ax, q - qb, run_end - qb, accI, accQ, tp); break;
+                case 3: run_chunks<3, CONV>(ax, q - qb, run_end - qb, accI, accQ, tp); break;
+                case 4: run_chunks<4, CONV>(ax, q - qb, run_end - qb, accI, accQ, tp); break;
                 default: break;
             }
             q = run_end;
             if (q - 1 == Es[0]) {                                  // the oldest window closes
-                if (s_ok) orow[k_head] = acc[0];
+                const float2 yi = unpack2(accI[0]), yq = unpack2(accQ[0]);
+                if (s_ok) orow[k_head] = make_float2(yi.x + yi.y, yq.x + yq.y);
                 k_head++;
 #pragma unroll
                 for (int j = 0; j + 1 < A_MAX; j++) {
-                    acc[j] = acc[j + 1];
+                    accI[j] = accI[j + 1];
+                    accQ[j] = accQ[j + 1];
                     tp[j] = tp[j + 1];
                     Es[j] = Es[j + 1];
                 }
@@ -244,10 +384,13 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
                 nact--;
             }
         }
-        __syncwarp();
-        if (lane == 0 && batch + BK_NST < n_batches) {
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // our reads before the next TMA write
-            issue(batch + BK_NST);
+        if (tb == 1 || bi == n_boxes - 1) {                          // slot consumed: refill it, move on
+            __syncwarp();
+            if (lane == 0 && (a - slot0) + NST < n_slots) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // our reads before the next TMA write
+                issue(a + NST, slot);
+            }
+            if (++slot == NST) { slot = 0; phase ^= 1; }
         }
     }
 }
@@ -292,11 +435,74 @@ bool encode_rows(CUtensorMap *m, const void *base, long n_cols, long n_rows, lon
     return true;
 }
 
+// 3-D view of the same rows: (32 samples, time blocks of 128 B, rows); box = (32, SLOT_BOXES, 32 rows)
+bool encode_rows3(CUtensorMap *m, const void *base, long n_blocks, long n_rows, long pitch)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[3] = {BOX_SAMPLES, (cuuint64_t)(n_blocks > 0 ? n_blocks : 1), (cuuint64_t)n_rows};
+    const cuuint64_t strides[2] = {BOX_SAMPLES * 4, (cuuint64_t)pitch * 4};
+    const cuuint32_t box[3] = {BOX_SAMPLES, SLOT_BOXES, BOX_ROWS};
+    const cuuint32_t es[3] = {1, 1, 1};
+    const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void *>(base), dims, strides, box, es,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("fused bank: cuTensorMapEncodeTiled (3-D) failed with CUresult " + std::to_string((int)r));
+        return false;
+    }
+    return true;
+}
+
+// ---- launch variants: warps per CTA, ring slots per warp, conversion flavour ----------------------------------
+struct BankVariant {
+    int warps, nst, conv;
+};
+typedef void (*BankKernel)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const BankParams);
+
+BankVariant bank_variant()
+{
+    static BankVariant v = [] {
+        BankVariant d{8, 2, 0};
+        if (const char *e = getenv("SFE_BANK_VARIANT")) {   // tuning hook: "warps,slots,conv"
+            int w = 0, n = 0, c = 0;
+            if (sscanf(e, "%d,%d,%d", &w, &n, &c) == 3) d = BankVariant{w, n, c};
+        }
+        return d;
+    }();
+    return v;
+}
+
+template <int W, int N>
+BankKernel bank_pick_conv(int conv)
+{
+    switch (conv) {
+        case 0: return fused_bank_kernel<W, N, 0>;
+        case 1: return fused_bank_kernel<W, N, 1>;
+        case 2: return fused_bank_kernel<W, N, 2>;
+        case 3: return fused_bank_kernel<W, N, 3>;
+        default: return nullptr;
+    }
+}
+
+BankKernel bank_pick(const BankVariant &v)
+{
+    const int key = v.warps * 10 + v.nst;
+    switch (key) {
+        case 62: return bank_pick_conv<6, 2>(v.conv);
+        case 63: return bank_pick_conv<6, 3>(v.conv);
+        case 82: return bank_pick_conv<8, 2>(v.conv);
+        case 102: return bank_pick_conv<10, 2>(v.conv);
+        default: return nullptr;
+    }
+}
+
 }  // namespace
 
 size_t bank_smem_bytes(int n_rows, int row_len)
 {
-    return (size_t)BK_WARPS * BK_NST * STAGE_BYTES + (size_t)n_rows * row_len * sizeof(float) + 1024;
+    const BankVariant v = bank_variant();
+    return (size_t)v.warps * v.nst * SLOT_BYTES + (size_t)n_rows * row_len * sizeof(float) + 1024;
 }
 
 int bank_max_live() { return A_MAX; }
@@ -309,21 +515,30 @@ int launch_bank(const BankParams &p_in, cudaStream_t st)
         set_error("fused bank: input rows must be int16 IQ, 16-byte aligned with a pitch that is a multiple of 4 samples");
         return SFE_ERR_ARG;
     }
-    CUtensorMap mc, mh;
-    if (!encode_rows(&mc, p.in.cur, p.in.n, p.n_streams, p.in.pitch) || !encode_rows(&mh, p.in.hist, p.H, p.n_streams, p.H))
+    const BankVariant v = bank_variant();
+    BankKernel kern = bank_pick(v);
+    if (!kern) {
+        set_error("fused bank: SFE_BANK_VARIANT names a variant that is not compiled in");
+        return SFE_ERR_ARG;
+    }
+    CUtensorMap mc, mh, mc3, mh3;
+    if (!encode_rows(&mc, p.in.cur, p.in.n, p.n_streams, p.in.pitch) || !encode_rows(&mh, p.in.hist, p.H, p.n_streams, p.H) ||
+        !encode_rows3(&mc3, p.in.cur, p.in.n / BOX_SAMPLES, p.n_streams, p.in.pitch) ||
+        !encode_rows3(&mh3, p.in.hist, p.H / BOX_SAMPLES, p.n_streams, p.H))
         return SFE_ERR_CUDA;
     int dev = 0, sms = 0;
     if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
     p.n_groups = (p.n_streams + BOX_ROWS - 1) / BOX_ROWS;
     // one work item per warp slot of the machine, but never fewer than 8 outputs per item
-    long n_seg = ((long)sms * BK_WARPS + p.n_groups - 1) / p.n_groups;
+    // (rounded down: one item too many would cost a whole second wave)
+    long n_seg = ((long)sms * v.warps) / p.n_groups;
     if (n_seg > p.n_out / 8) n_seg = p.n_out / 8;
     if (n_seg < 1) n_seg = 1;
     p.n_seg = (int)n_seg;
     const long items = (long)p.n_groups * p.n_seg;
     const size_t smem = bank_smem_bytes(p.n_rows, p.row_len);
-    if (!SFE_CUDA(cudaFuncSetAttribute(fused_bank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
-    fused_bank_kernel<<<(unsigned)((items + BK_WARPS - 1) / BK_WARPS), BK_WARPS * 32, smem, st>>>(mc, mh, p);
+    if (!SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
+    kern<<<(unsigned)((items + v.warps - 1) / v.warps), v.warps * 32, smem, st>>>(mc, mh, mc3, mh3, p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }

@@ -2,6 +2,7 @@
 // (compiled with -ffp-contract=off by simplefe_b200/build.py).
 #include "schedule.h"
 #include <cmath>
+#include <cstring>
 
 namespace sfe {
 
@@ -39,26 +40,72 @@ int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t 
     return n_out;
 }
 
-void walk_batch(WalkState &st, int up, int blk, float rate, int64_t n_in, Schedule &s)
+void walk_batch(WalkState &st, int up, int blk, float rate, int64_t n_in, Schedule &s, bool want_entries)
 {
     s.e.clear();
-    const int out_len = (int)floorf((float)blk / rate) + 2;
-    for (int64_t off = 0; off < n_in; off += blk) {
-        const int n = (int)((n_in - off) < blk ? (n_in - off) : blk);
-        walk_call(st, up, n, out_len, rate, off, s.e);
-    }
+    s.count = 0;
     s.uniform = false;
     s.pos0 = s.step = 0;
-    const size_t m = s.e.size();
-    if (m == 0) return;
-    bool uni = true;
-    const int64_t p0 = s.e[0].pos;
-    const int64_t d = m > 1 ? (int64_t)s.e[1].pos - p0 : (int64_t)llroundf(rate * (float)up);
-    for (size_t k = 0; k < m && uni; k++)
-        uni = (s.e[k].mu == 0.0f) && ((int64_t)s.e[k].pos == p0 + (int64_t)k * d);
+    const int out_len = (int)floorf((float)blk / rate) + 2;
+    if (s.memo_up != up || s.memo_out_len != out_len || s.memo_rate != rate || s.memo.size() > 4096) {
+        s.memo.clear();   // other parameters, or a fractional rate whose states never repeat
+        s.memo_up = up;
+        s.memo_out_len = out_len;
+        s.memo_rate = rate;
+    }
+    bool uni = true, have_prev = false;
+    int64_t d = 0, prev = 0, first = 0;
+    for (int64_t off = 0; off < n_in; off += blk) {
+        const int n = (int)((n_in - off) < blk ? (n_in - off) : blk);
+        uint32_t mu_bits;
+        memcpy(&mu_bits, &st.mu, 4);
+        const auto key = std::make_tuple(st.pos, mu_bits, st.held, n);
+        auto it = s.memo.find(key);
+        if (it == s.memo.end()) {
+            CallMemo m;
+            WalkState w = st;
+            walk_call(w, up, n, out_len, rate, 0, m.e);
+            m.after = w;
+            for (size_t k = 0; k < m.e.size(); k++) {
+                m.mu0 = m.mu0 && m.e[k].mu == 0.0f;
+                if (k == 1) m.d = (int64_t)m.e[1].pos - m.e[0].pos;
+                if (k >= 1) m.arith = m.arith && ((int64_t)m.e[k].pos - m.e[k - 1].pos == m.d);
+            }
+            it = s.memo.emplace(key, std::move(m)).first;
+        }
+        const CallMemo &m = it->second;
+        st = m.after;
+        const size_t cnt = m.e.size();
+        if (cnt == 0) continue;
+        const int64_t base = off * (int64_t)up;
+        if (want_entries) {
+            const size_t at = s.e.size();
+            s.e.resize(at + cnt);
+            for (size_t k = 0; k < cnt; k++) s.e[at + k] = SchedEntry{(int32_t)(base + m.e[k].pos), m.e[k].mu};
+        }
+        // uniformity of the batch from the calls' summaries
+        uni = uni && m.mu0 && m.arith;
+        const int64_t f = base + m.e.front().pos, l = base + m.e.back().pos;
+        if (cnt >= 2) {
+            if (d == 0) d = m.d;
+            else uni = uni && d == m.d;
+        }
+        if (have_prev) {
+            const int64_t gap = f - prev;
+            if (d == 0) d = gap;
+            else uni = uni && gap == d;
+        } else {
+            first = f;
+        }
+        have_prev = true;
+        prev = l;
+        s.count += (int64_t)cnt;
+    }
+    if (s.count == 0) return;
+    if (s.count == 1) d = (int64_t)llroundf(rate * (float)up);
     if (uni && d > 0) {
         s.uniform = true;
-        s.pos0 = p0;
+        s.pos0 = first;
         s.step = d;
     }
 }

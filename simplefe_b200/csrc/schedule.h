@@ -8,6 +8,8 @@
 // exact single-precision recurrence so that output counts and sample indices are bit-exact.
 #pragma once
 #include <cstdint>
+#include <map>
+#include <tuple>
 #include <vector>
 
 namespace sfe {
@@ -25,10 +27,25 @@ struct SchedEntry {
     float mu;             // out = s(pos)*(1-mu) + mu*s(pos+1)
 };
 
+// what one reference process() call does from a given state: memoised, because for integral steps the
+// state (pos, mu, held) cycles through a handful of values and a batch is thousands of identical calls
+struct CallMemo {
+    std::vector<SchedEntry> e;  // entries relative to the call's first sample (base_in = 0)
+    WalkState after;
+    bool mu0 = true;            // all mu == 0
+    bool arith = true;          // positions form an arithmetic progression
+    int64_t d = 0;              // its difference (n >= 2)
+};
+
 struct Schedule {
-    std::vector<SchedEntry> e;  // one per output, in output order
+    std::vector<SchedEntry> e;  // one per output, in output order (empty in summary mode)
+    int64_t count = 0;          // number of outputs of the batch
     bool uniform = false;       // all mu == 0 and pos = pos0 + k*step
     int64_t pos0 = 0, step = 0;
+    // key: (pos, mu bits, held, n_in of the call); parameters (up, out_len, rate) are fixed per owner
+    std::map<std::tuple<int, uint32_t, bool, int>, CallMemo> memo;
+    int memo_up = 0, memo_out_len = 0;
+    float memo_rate = 0.f;
 };
 
 // One reference process() call: appends the outputs of a call with n_in samples whose first
@@ -37,6 +54,8 @@ int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t 
               std::vector<SchedEntry> &out);
 
 // A batch of n_in samples fed as ceil(n_in/blk) calls of blk samples, out_len = floor(blk/rate)+2.
-void walk_batch(WalkState &st, int up, int blk, float rate, int64_t n_in, Schedule &s);
+// want_entries = false (summary mode): only count / uniform / pos0 / step are produced -- all that the
+// closed-form kernels need -- and a batch costs O(calls) host time instead of O(outputs).
+void walk_batch(WalkState &st, int up, int blk, float rate, int64_t n_in, Schedule &s, bool want_entries = true);
 
 }  // namespace sfe

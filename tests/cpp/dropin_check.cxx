@@ -80,11 +80,13 @@ int main()
     {   // ring: simple write/read, wrap-around with conversion, refusal when full / short
         ring_buffer<float> rb(8);
         float a[6] = {1, 2, 3, 4, 5, 6}, out[8];
-        printf("ring w %d space %d count %d\n", rb.write(a, 6), rb.get_space(), rb.get_count());
+        int w = rb.write(a, 6);   // (separate statements: argument evaluation order is unspecified)
+        printf("ring w %d space %d count %d\n", w, rb.get_space(), rb.get_count());
         printf("ring w_full %d\n", rb.write(a, 3));
         int n = rb.read(out, 4 * sizeof(float), conv_copy, len_floats);
         printf("ring r %d : %g %g %g %g\n", n, out[0], out[1], out[2], out[3]);
-        printf("ring w_wrap %d count %d\n", rb.write(a, 5), rb.get_count());
+        w = rb.write(a, 5);
+        printf("ring w_wrap %d count %d\n", w, rb.get_count());
         n = rb.read(out, 7 * sizeof(float), conv_copy, len_floats);
         printf("ring r_wrap %d : %g %g %g %g %g %g %g\n", n, out[0], out[1], out[2], out[3], out[4], out[5], out[6]);
         printf("ring r_short %d\n", rb.read(out, 4, conv_copy, len_floats));

@@ -65,10 +65,19 @@ def test_schedule_matches_oracle_counts():
 #include "schedule.h"
 #include <cstdio>
 #include <cstdlib>
+#include <cmath>
 int main(int argc, char** argv) {
   int up = atoi(argv[1]), blk = atoi(argv[2]); float rate = (float)atof(argv[3]); long n = atol(argv[4]);
-  sfe::WalkState st; sfe::Schedule s;
+  sfe::WalkState st, st2; sfe::Schedule s, s2;
   for (int rep = 0; rep < 3; rep++) { sfe::walk_batch(st, up, blk, rate, n, s);
+    sfe::walk_batch(st2, up, blk, rate, n, s2, false);   // summary mode must agree with the full walk
+    if (s2.count != (long)s.e.size() || s2.uniform != s.uniform || s2.pos0 != s.pos0 || s2.step != s.step || !s2.e.empty() ||
+        st2.pos != st.pos || st2.mu != st.mu || st2.held != st.held) { printf("SUMMARY MISMATCH\n"); return 1; }
+    // and with the unmemoised reference walk, call by call
+    { static sfe::WalkState st3; std::vector<sfe::SchedEntry> e3; int ol = (int)floorf((float)blk / rate) + 2;
+      for (long off = 0; off < n; off += blk) sfe::walk_call(st3, up, (int)((n - off) < blk ? (n - off) : blk), ol, rate, off, e3);
+      if (e3.size() != s.e.size()) { printf("MEMO MISMATCH\n"); return 1; }
+      for (size_t k = 0; k < e3.size(); k++) if (e3[k].pos != s.e[k].pos || e3[k].mu != s.e[k].mu) { printf("MEMO MISMATCH\n"); return 1; } }
     printf("%zu %d %ld %ld", s.e.size(), (int)s.uniform, (long)s.pos0, (long)s.step);
     unsigned long long h = 1469598103934665603ull;
     for (auto& e : s.e) { h = (h ^ (unsigned)e.pos) * 1099511628211ull; unsigned m; __builtin_memcpy(&m, &e.mu, 4); h = (h ^ m) * 1099511628211ull; }
