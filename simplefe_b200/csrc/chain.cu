@@ -64,7 +64,7 @@ struct Op {
     std::vector<double> g;         // pre-stage FIR at the raw rate (double)
     std::vector<float> r;          // bank stage taps as the reference ctor pads them
     std::map<int, float *> d_tables;  // bank tables by alignment key (bank_table)
-    int row_len = 0, n_rows = 0, rows_per_phase = 1;
+    int row_len = 0, n_rows = 0, rows_per_phase = 1, nc = 0, n_live = 1;
     long n_first = 0;
     bool bad_sched = false;
     // per call
@@ -323,6 +323,8 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             p.H = op.H;
             p.table = it->second;
             p.row_len = op.row_len;
+            p.nc = op.nc;
+            p.n_live = op.n_live;
             p.n_rows = op.n_rows;
             p.rows_per_phase = op.rows_per_phase;
             rc = launch_bank(p, st);
@@ -456,14 +458,18 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
             }
             const int J = ((int)op.r.size() + op.up - 1) / op.up;
             const int Tc = op.D * (J - 1) + (int)op.g.size();
-            const int NC = (Tc + 6) / 4;
-            op.row_len = 4 * NC;
+            const int NC = bank_nc(Tc);
+            op.nc = NC;
+            op.row_len = bank_row_len(Tc);
             op.rows_per_phase = op.D % 4 == 0 ? 1 : 4;
             op.n_rows = op.up * op.rows_per_phase;
             const long spacing = (long)op.D * (step_b / op.up);          // samples between consecutive outputs, at least
-            const long live = spacing >= 8 ? (NC - 1) / (spacing / 4) + 1 : 1 << 30;
+            // windows open and close on 32-sample box boundaries: at most one may open per box, and a box is
+            // overlapped by the windows whose first chunk lies in a range of NC + 7 chunks
+            const long live = spacing >= 64 ? (NC + 6) / (spacing / 4) + 1 : 1 << 30;
             if (live <= bank_max_live() && bank_smem_bytes(op.n_rows, op.row_len) <= 227 * 1024) {
-                op.H = (op.row_len + 2 * op.D + 4 + 31) / 32 * 32;
+                op.n_live = (int)live;
+                op.H = (4 * NC + 2 * op.D + 4 + 31) / 32 * 32;
                 op.name = std::string("bank_fused(") + (has_bc ? "blkconv*" : "") + (has_b ? "decim*" : "") + "polyphase)/L" +
                           std::to_string(op.up) + "D" + std::to_string(op.D) + "T" + std::to_string(Tc);
                 c->plan = op.name;

@@ -35,7 +35,8 @@ constexpr int BOX_SAMPLES = 32, BOX_ROWS = 32;
 constexpr int BOX_BYTES = BOX_SAMPLES * BOX_ROWS * 4;   // one TMA box = one ring slot = 8 chunks of 4 samples per lane
 constexpr int SLOT_BOXES = 2;         // boxes (time blocks of 128 B per row) fetched by one TMA instruction
 constexpr int SLOT_BYTES = SLOT_BOXES * BOX_BYTES;
-constexpr int A_MAX = 4;             // live outputs per lane
+constexpr int A_MAX = 4;             // window slots per lane, at most
+constexpr int PAD_CHUNKS = 8;        // zero chunks in front of and behind the taps of every table row
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -155,10 +156,10 @@ __device__ __forceinline__ void convert4(const uint4 &w, f32x2 &i01, f32x2 &i23,
     }
 }
 
-// one chunk (4 samples of this lane's stream) into NA live windows.  Accumulators hold (even, odd) partial sums:
-// the pair of consecutive samples meets the pair of consecutive taps in one FFMA2.
+// one chunk (4 samples of this lane's stream) into the NA window slots.  Accumulators hold (even, odd) partial
+// sums: the pair of consecutive samples meets the pair of consecutive taps in one FFMA2.
 template <int NA, int CONV, int TOFF>
-__device__ __forceinline__ void chunk(uint32_t addr, f32x2 (&accI)[A_MAX], f32x2 (&accQ)[A_MAX], const uint32_t (&tp)[A_MAX])
+__device__ __forceinline__ void chunk(uint32_t addr, f32x2 (&accI)[NA], f32x2 (&accQ)[NA], const uint32_t (&tp)[NA])
 {
     const uint4 w = lds_u4(addr);
     f32x2 i01, i23, q01, q23;
@@ -174,29 +175,21 @@ __device__ __forceinline__ void chunk(uint32_t addr, f32x2 (&accI)[A_MAX], f32x2
     }
 }
 
-// chunks [c0, c1) of the current box (0 <= c0 < c1 <= 8).  ax = slot base | lane row | (lane & 7) << 4: the 16-byte
-// slot of chunk c inside this lane's 128-byte row is c ^ (lane & 7) (SWIZZLE_128B), i.e. address ax ^ (c << 4).
+// one whole box (8 chunks) of this lane's 128-byte line.  ax carries the SWIZZLE_128B term (line & 7) << 4 in
+// bits 4-6: chunk c sits at ax ^ (c << 4).  Every window slot advances by 8 chunks of taps.
 template <int NA, int CONV>
-__device__ __forceinline__ void run_chunks(uint32_t ax, int c0, int c1, f32x2 (&accI)[A_MAX], f32x2 (&accQ)[A_MAX], uint32_t (&tp)[A_MAX])
+__device__ __forceinline__ void run_box(uint32_t ax, f32x2 (&accI)[NA], f32x2 (&accQ)[NA], uint32_t (&tp)[NA])
 {
-    if (c0 == 0 && c1 == 8) {            // a whole box without events: the common case, fully unrolled
-        chunk<NA, CONV, 0>(ax, accI, accQ, tp);
-        chunk<NA, CONV, 16>(ax ^ 0x10u, accI, accQ, tp);
-        chunk<NA, CONV, 32>(ax ^ 0x20u, accI, accQ, tp);
-        chunk<NA, CONV, 48>(ax ^ 0x30u, accI, accQ, tp);
-        chunk<NA, CONV, 64>(ax ^ 0x40u, accI, accQ, tp);
-        chunk<NA, CONV, 80>(ax ^ 0x50u, accI, accQ, tp);
-        chunk<NA, CONV, 96>(ax ^ 0x60u, accI, accQ, tp);
-        chunk<NA, CONV, 112>(ax ^ 0x70u, accI, accQ, tp);
+    chunk<NA, CONV, 0>(ax, accI, accQ, tp);
+    chunk<NA, CONV, 16>(ax ^ 0x10u, accI, accQ, tp);
+    chunk<NA, CONV, 32>(ax ^ 0x20u, accI, accQ, tp);
+    chunk<NA, CONV, 48>(ax ^ 0x30u, accI, accQ, tp);
+    chunk<NA, CONV, 64>(ax ^ 0x40u, accI, accQ, tp);
+    chunk<NA, CONV, 80>(ax ^ 0x50u, accI, accQ, tp);
+    chunk<NA, CONV, 96>(ax ^ 0x60u, accI, accQ, tp);
+    chunk<NA, CONV, 112>(ax ^ 0x70u, accI, accQ, tp);
 #pragma unroll
-        for (int j = 0; j < NA; j++) tp[j] += 128;
-    } else {
-        for (int c = c0; c < c1; c++) {
-            chunk<NA, CONV, 0>(ax ^ ((uint32_t)c << 4), accI, accQ, tp);
-#pragma unroll
-            for (int j = 0; j < NA; j++) tp[j] += 16;
-        }
-    }
+    for (int j = 0; j < NA; j++) tp[j] += 128;
 }
 
 struct OutInfo {
@@ -221,7 +214,7 @@ __device__ __forceinline__ void split_pos(const BankParams &p, long k, long &M, 
     if (ph < 0) { ph += p.L; M -= 1; }                    // floor division: pos = -1 is a held-over output
 }
 
-template <int WARPS, int NST, int CONV>
+template <int WARPS, int NST, int CONV, int NLIVE>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_constant__ CUtensorMap map_hist,
                   const __grid_constant__ CUtensorMap map_cur3, const __grid_constant__ CUtensorMap map_hist3, const BankParams p)
@@ -255,7 +248,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     const int g = (int)(item % p.n_groups), seg = (int)(item / p.n_groups);
     const long k_lo = p.n_out * seg / p.n_seg, k_hi = p.n_out * (seg + 1) / p.n_seg;
     if (k_lo >= k_hi) return;
-    const int NC = p.row_len >> 2;
+    const int NC = p.nc;
     const int row_bytes = p.row_len * 4;
 
     long M_next;
@@ -306,20 +299,24 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     if (lane == 0)
         for (int b = 0; b < NST && b < n_slots; b++) issue(slot0 + b, b);
 
-    // ---- live outputs (slot 0 finishes first) ---------------------------------------------------------
-    f32x2 accI[A_MAX], accQ[A_MAX];
-    uint32_t tp[A_MAX];
-    int Es[A_MAX];
+    // ---- window slots (slot 0 closes first) ------------------------------------------------------------
+    // Every table row carries PAD_CHUNKS zero chunks in front of and behind its taps, so a window may start at
+    // the beginning of the box that holds its first sample and run to the end of the box that holds its last
+    // one: all bookkeeping happens between boxes and every box is the same straight-line code over NLIVE slots.
+    // A slot without a window rests on the zero pad of row 0.
+    f32x2 accI[NLIVE], accQ[NLIVE];
+    uint32_t tp[NLIVE];
+    int Eb[NLIVE];                                                 // box in which the slot's window ends
 #pragma unroll
-    for (int j = 0; j < A_MAX; j++) {
+    for (int j = 0; j < NLIVE; j++) {
         accI[j] = accQ[j] = 0ull;
         tp[j] = table_a;
-        Es[j] = 0x3fffffff;
+        Eb[j] = 0x3fffffff;
     }
     int nact = 0;
     long k_next = k_lo, k_head = k_lo;
     OutInfo nxt = first;
-    int S_next = q_begin;
+    int open_box = box0;
     const int sM = (int)(p.step / p.L), sP = (int)(p.step % p.L);   // schedule stepping without division
     const int s_row = g * BOX_ROWS + lane;
     float2 *orow = p.out + (long)s_row * p.out_pitch;
@@ -330,60 +327,49 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     for (int bi = 0; bi < n_boxes; bi++) {
         const int B = box0 + bi, a = B >> 1, tb = B & 1;
         if (bi == 0 || tb == 0) mbar_wait(bar0 + 8 * slot, phase);   // first box of a slot
-        const int qb = B << 3;                                       // first chunk of this box
-        // this lane's 128-byte line of the box, with the SWIZZLE_128B term (line index & 7) << 4 in bits 4-6:
-        // chunk c sits at ax ^ (c << 4).  3-D slot: lines (2 lane + tb); 2-D boxes: box tb, line lane.
-        const uint32_t line = slot_3d(a) ? (uint32_t)(2 * lane + tb) : (uint32_t)(tb * BOX_ROWS + lane);
-        const uint32_t ax = ring_a + slot * SLOT_BYTES + line * 128u + ((line & 7u) << 4);
-        int q = qb > q_begin ? qb : q_begin;
-        const int q_stop = (qb + 8) <= q_end + 1 ? (qb + 8) : q_end + 1;
-        while (q < q_stop) {
-            if (q == S_next) {                                     // a window opens (at most one per chunk)
+        if (B == open_box) {                                         // a window opens in this box (at most one)
+            const int S = nxt.E - NC + 1;                            // its first chunk
+            const uint32_t t0 = table_a + (uint32_t)(nxt.row * row_bytes) + (uint32_t)(PAD_CHUNKS - (S & 7)) * 16u;
 #pragma unroll
-                for (int j = 0; j < A_MAX; j++)
-                    if (j == nact) {
-                        accI[j] = accQ[j] = 0ull;
-                        tp[j] = table_a + (uint32_t)(nxt.row * row_bytes);
-                        Es[j] = nxt.E;
-                    }
-                nact++;
-                k_next++;
-                if (k_next < k_hi) {
-                    ph_next += sP;
-                    M_next += sM;
-                    if (ph_next >= p.L) { ph_next -= p.L; M_next += 1; }
-                    nxt = out_info(p, M_next, ph_next);
-                    S_next = nxt.E - NC + 1;
-                } else {
-                    S_next = 0x3fffffff;
+            for (int j = 0; j < NLIVE; j++)
+                if (j == nact) {
+                    accI[j] = accQ[j] = 0ull;
+                    tp[j] = t0;
+                    Eb[j] = nxt.E >> 3;
                 }
-            }
-            // chunks [q, run_end): no window opens, the oldest one may close with the last chunk
-            int run_end = q_stop < S_next ? q_stop : S_next;
-            if (Es[0] + 1 < run_end) run_end = Es[0] + 1;
-            switch (nact) {
-                case 1: run_chunks<1, CONV>(ax, q - qb, run_end - qb, accI, accQ, tp); break;
-                case 2: run_chunks<2, CONV>(ax, q - qb, run_end - qb, accI, accQ, tp); break;
-                case 3: run_chunks<3, CONV>(ax, q - qb, run_end - qb, accI, accQ, tp); break;
-                case 4: run_chunks<4, CONV>(ax, q - qb, run_end - qb, accI, accQ, tp); break;
-                default: break;
-            }
-            q = run_end;
-            if (q - 1 == Es[0]) {                                  // the oldest window closes
-                const float2 yi = unpack2(accI[0]), yq = unpack2(accQ[0]);
-                if (s_ok) orow[k_head] = make_float2(yi.x + yi.y, yq.x + yq.y);
-                k_head++;
-#pragma unroll
-                for (int j = 0; j + 1 < A_MAX; j++) {
-                    accI[j] = accI[j + 1];
-                    accQ[j] = accQ[j + 1];
-                    tp[j] = tp[j + 1];
-                    Es[j] = Es[j + 1];
-                }
-                Es[A_MAX - 1] = 0x3fffffff;
-                nact--;
+            nact++;
+            k_next++;
+            if (k_next < k_hi) {
+                ph_next += sP;
+                M_next += sM;
+                if (ph_next >= p.L) { ph_next -= p.L; M_next += 1; }
+                nxt = out_info(p, M_next, ph_next);
+                open_box = (nxt.E - NC + 1) >> 3;
+            } else {
+                open_box = 0x3fffffff;
             }
         }
+        // this lane's 128-byte line of the box: 3-D slot: line 2 lane + tb; 2-D boxes: box tb, line lane
+        const uint32_t line = slot_3d(a) ? (uint32_t)(2 * lane + tb) : (uint32_t)(tb * BOX_ROWS + lane);
+        const uint32_t ax = ring_a + slot * SLOT_BYTES + line * 128u + ((line & 7u) << 4);
+        run_box<NLIVE, CONV>(ax, accI, accQ, tp);
+        if (B == Eb[0]) {                                            // the oldest window is complete
+            const float2 yi = unpack2(accI[0]), yq = unpack2(accQ[0]);
+            if (s_ok) orow[k_head] = make_float2(yi.x + yi.y, yq.x + yq.y);
+            k_head++;
+#pragma unroll
+            for (int j = 0; j + 1 < NLIVE; j++) {
+                accI[j] = accI[j + 1];
+                accQ[j] = accQ[j + 1];
+                tp[j] = tp[j + 1];
+                Eb[j] = Eb[j + 1];
+            }
+            Eb[NLIVE - 1] = 0x3fffffff;
+            nact--;
+        }
+#pragma unroll
+        for (int j = 0; j < NLIVE; j++)
+            if (j >= nact) tp[j] = table_a;                          // idle slots stay on the zero pad
         if (tb == 1 || bi == n_boxes - 1) {                          // slot consumed: refill it, move on
             __syncwarp();
             if (lane == 0 && (a - slot0) + NST < n_slots) {
@@ -463,7 +449,7 @@ typedef void (*BankKernel)(const CUtensorMap, const CUtensorMap, const CUtensorM
 BankVariant bank_variant()
 {
     static BankVariant v = [] {
-        BankVariant d{8, 2, 0};
+        BankVariant d{8, 2, 2};
         if (const char *e = getenv("SFE_BANK_VARIANT")) {   // tuning hook: "warps,slots,conv"
             int w = 0, n = 0, c = 0;
             if (sscanf(e, "%d,%d,%d", &w, &n, &c) == 3) d = BankVariant{w, n, c};
@@ -473,26 +459,28 @@ BankVariant bank_variant()
     return v;
 }
 
-template <int W, int N>
-BankKernel bank_pick_conv(int conv)
+template <int W, int N, int C>
+BankKernel bank_pick_live(int live)
 {
-    switch (conv) {
-        case 0: return fused_bank_kernel<W, N, 0>;
-        case 1: return fused_bank_kernel<W, N, 1>;
-        case 2: return fused_bank_kernel<W, N, 2>;
-        case 3: return fused_bank_kernel<W, N, 3>;
+    switch (live) {
+        case 1: return fused_bank_kernel<W, N, C, 1>;
+        case 2: return fused_bank_kernel<W, N, C, 2>;
+        case 3: return fused_bank_kernel<W, N, C, 3>;
+        case 4: return fused_bank_kernel<W, N, C, 4>;
         default: return nullptr;
     }
 }
 
-BankKernel bank_pick(const BankVariant &v)
+BankKernel bank_pick(const BankVariant &v, int live)
 {
-    const int key = v.warps * 10 + v.nst;
+    const int key = v.warps * 100 + v.nst * 10 + v.conv;
     switch (key) {
-        case 62: return bank_pick_conv<6, 2>(v.conv);
-        case 63: return bank_pick_conv<6, 3>(v.conv);
-        case 82: return bank_pick_conv<8, 2>(v.conv);
-        case 102: return bank_pick_conv<10, 2>(v.conv);
+        case 820: return bank_pick_live<8, 2, 0>(live);
+        case 822: return bank_pick_live<8, 2, 2>(live);
+        case 1020: return bank_pick_live<10, 2, 0>(live);
+        case 1021: return bank_pick_live<10, 2, 1>(live);
+        case 1022: return bank_pick_live<10, 2, 2>(live);
+        case 1023: return bank_pick_live<10, 2, 3>(live);
         default: return nullptr;
     }
 }
@@ -506,6 +494,8 @@ size_t bank_smem_bytes(int n_rows, int row_len)
 }
 
 int bank_max_live() { return A_MAX; }
+int bank_nc(int Tc) { return (Tc + 6) / 4; }
+int bank_row_len(int Tc) { return 4 * (bank_nc(Tc) + 2 * PAD_CHUNKS); }
 
 int launch_bank(const BankParams &p_in, cudaStream_t st)
 {
@@ -516,9 +506,9 @@ int launch_bank(const BankParams &p_in, cudaStream_t st)
         return SFE_ERR_ARG;
     }
     const BankVariant v = bank_variant();
-    BankKernel kern = bank_pick(v);
+    BankKernel kern = bank_pick(v, p.n_live);
     if (!kern) {
-        set_error("fused bank: SFE_BANK_VARIANT names a variant that is not compiled in");
+        set_error("fused bank: SFE_BANK_VARIANT names a variant that is not compiled in (or n_live is out of range)");
         return SFE_ERR_ARG;
     }
     CUtensorMap mc, mh, mc3, mh3;
@@ -551,8 +541,8 @@ void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r
 {
     const int J = ((int)r.size() + L - 1) / L;
     const int Tc = D * (J - 1) + (int)g.size();
-    const int NC = (Tc + 3 + 3) / 4;
-    const int RL = 4 * NC;
+    const int NC = bank_nc(Tc);
+    const int RL = bank_row_len(Tc);              // zero pads: windows open and close on box boundaries (kernel)
     const int per = e_only >= 0 ? 1 : 4;
     rows.assign((size_t)L * per * RL, 0.f);
     std::vector<double> c((size_t)Tc);
@@ -566,9 +556,9 @@ void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r
         for (int v = 0; v < per; v++) {
             const int e = e_only >= 0 ? e_only : v;
             float *row = rows.data() + ((size_t)ph * per + v) * RL;
-            for (int i = 0; i < RL; i++) {
-                const int u = RL - 4 + e - i;
-                if (u >= 0 && u < Tc) row[i] = (float)(c[u] * scale);
+            for (int i = 0; i < 4 * NC; i++) {
+                const int u = 4 * NC - 4 + e - i;
+                if (u >= 0 && u < Tc) row[4 * PAD_CHUNKS + i] = (float)(c[u] * scale);
             }
         }
     }

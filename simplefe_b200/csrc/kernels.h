@@ -93,11 +93,15 @@ struct BankParams {
     long n_first;         // raw index of decimated sample 0 of this call
     int H;                // history depth in samples, multiple of 32
     const float *table;   // device: n_rows rows of row_len floats (bank_table)
-    int row_len, n_rows;
+    int row_len, n_rows;  // row_len = 4 * (nc + 2 * pad chunks): bank_row_len()
+    int nc;               // chunks (4 samples) of taps per row
+    int n_live;           // window slots per lane: the most windows that ever overlap one 32-sample box
     int rows_per_phase;   // 1: one alignment per call (D % 4 == 0), 4: row = ph*4 + alignment
     // filled by launch_bank
     int n_groups, n_seg;
 };
+int bank_nc(int Tc);                  // chunks of taps for a composite filter of Tc taps (any alignment)
+int bank_row_len(int Tc);             // floats per table row, zero pads included
 void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r, int L, double scale, int e_only,
                 std::vector<float> &rows, int *row_len, int *n_rows, int *Tc);
 size_t bank_smem_bytes(int n_rows, int row_len);
