@@ -1,0 +1,124 @@
+#!/usr/bin/env python
+"""bench_stages.py -- secondary report: every BASELINE.json config and every kernel plan, one GPU.
+
+bench.py is the contract (cfg 5, one JSON line).  This script fills BASELINE.md's table: for each config of
+SURVEY.md 8-d it times the device-resident call (CUDA events on the launching stream, best-of after warm-up),
+names the kernels the chain picked, and reports algorithmic GB/s against the measured HBM peak.  Single-stream
+configs are launch-latency bound by construction, so each also runs batched.
+
+    python bench_stages.py [--quick] > gpurun_out/stages.json
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import fixtures as F  # noqa: E402
+
+FLAG_EXACT, FLAG_NO_FUSE, FLAG_NO_TENSOR, FLAG_NO_BANK = 1, 2, 4, 8
+
+
+def bytes_alg(cfg, n_in, n_out):
+    """first read of the input + final write of the output, per stream"""
+    return n_in * {F.IN_I16: 4, F.IN_U8: 2, F.IN_F32: 8}[cfg["in_fmt"]] + n_out * 8
+
+
+def run_case(name, cfg, S, N, flags, steps, warmup, peak, torch, Chain):
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev)
+    g.manual_seed(cfg["seed"])
+    if cfg["in_fmt"] == F.IN_I16:
+        d_in = torch.empty((S, N, 2), dtype=torch.int16, device=dev)
+        rows = max(1, (128 << 20) // (N * 8))
+        for s0 in range(0, S, rows):
+            blk = torch.randn((min(rows, S - s0), N, 2), generator=g, device=dev) * 0.25
+            d_in[s0:s0 + rows] = torch.round(blk.clamp_(-1, 1) * 32767.0).to(torch.int16)
+        del blk
+    else:
+        d_in = (torch.randn((S, N, 2), generator=g, device=dev) * 0.25).clamp_(-1, 1)
+    ch = Chain(S, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), flags=flags, device=0)
+    cap = ch.max_out(N)
+    d_out = torch.zeros((S, cap, 2), dtype=torch.float32, device=dev)
+    st = torch.cuda.current_stream()
+
+    def step():
+        return ch.process_dev(d_in.data_ptr(), N, N, d_out.data_ptr(), cap, st.cuda_stream)
+
+    for _ in range(warmup):
+        n_out = step()
+    torch.cuda.synchronize()
+    ch.profile(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(steps):
+        n_out = step()
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    ch.profile(False)
+    prof = ch.profile_read()
+    b = bytes_alg(cfg, N, n_out) * S
+    res = {"case": name, "streams": S, "samples_per_stream": N, "outputs_per_stream": n_out, "plan": ch.plan,
+           "ms_per_step": ms, "Msamples_per_s": S * N / ms / 1e3, "bytes_alg_per_sample": b / (S * N),
+           "alg_GBps": b / ms / 1e6, "frac_of_measured_hbm": b / ms / 1e6 / peak,
+           "kernels": [{"name": n, "ms": m} for n, m, _ in prof]}
+    del ch, d_in, d_out
+    torch.cuda.empty_cache()
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    import torch
+    import simplefe_b200  # noqa: F401
+    from simplefe_b200.chain import Chain
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        peak = 6650.0
+    C = F.CONFIGS
+    big = 1 << 20
+    cases = [
+        # name, config, S, N, flags
+        ("cfg1 blkconv c64 (single stream)", C["cfg1"], 1, big, 0),
+        ("cfg1 blkconv c64 x256 streams", C["cfg1"], 256, big, 0),
+        ("cfg1' blkconv int16 x512 streams", dict(C["cfg1"], in_fmt=F.IN_I16), 512, big, 0),
+        ("cfg2 decimate/8 int16 (single stream, 10 MS)", C["cfg2"], 1, 10_000_000, 0),
+        ("cfg2 decimate/8 int16 x1024 streams [tcgen05 Toeplitz]", C["cfg2"], 1024, big, 0),
+        ("cfg2 decimate/8 int16 x1024 streams [CUDA-core FIR]", C["cfg2"], 1024, big, FLAG_NO_TENSOR),
+        ("cfg3 resample 3/625 int16 (single stream, 10 MS)", C["cfg3"], 1, 10_000_000, 0),
+        ("cfg3 resample 3/625 int16 x1024 streams [bank]", C["cfg3"], 1024, big, 0),
+        ("cfg3 resample 3/625 int16 x1024 streams [generic]", C["cfg3"], 1024, big, FLAG_NO_BANK),
+        ("cfg4 bpsk chain, fractional rates (single stream)", C["cfg4"], 1, 1_000_000, 0),
+        ("cfg4 bpsk chain, fractional rates x256 streams", C["cfg4"], 256, 1_000_000, 0),
+        ("cfg5 chain x1024 [one fused bank kernel]", C["cfg5"], 1024, big, 0),
+        ("cfg5 chain x1024 [fused blkconv*decim on tcgen05 + generic resample]", C["cfg5"], 1024, big, FLAG_NO_BANK),
+        ("cfg5 chain x1024 [fused blkconv*decim CUDA-core FIR + generic]", C["cfg5"], 1024, big, FLAG_NO_BANK | FLAG_NO_TENSOR),
+        ("cfg5 chain x256 [stage by stage: FFT blkconv, FIR, generic]", C["cfg5"], 256, big, FLAG_NO_BANK | FLAG_NO_FUSE | FLAG_NO_TENSOR),
+    ]
+    out = []
+    for name, cfg, S, N, flags in cases:
+        if args.only and args.only not in name:
+            continue
+        steps, warmup = (3, 2) if args.quick else (10, 3)
+        try:
+            r = run_case(name, cfg, S, N, flags, steps, warmup, peak, torch, Chain)
+        except Exception as ex:  # report, keep going
+            r = {"case": name, "error": repr(ex)}
+        out.append(r)
+        print(json.dumps(r), file=sys.stderr, flush=True)
+    print(json.dumps({"hbm_peak_GBps": peak, "cases": out}, indent=1))
+
+
+if __name__ == "__main__":
+    main()
