@@ -171,6 +171,24 @@ int sfe_ring_read(sfe_ring *r, void *dst, unsigned dst_len, sfe_ring_conv_fn con
    engine as the consumer. */
 int sfe_ring_read_dev(sfe_ring *r, void *d_dst, int n, void *stream);
 
+/* ---- (4) batched BPSK transmit path: examples/bpsk/bpsk.cxx:122-174 for many channels (additive) -------- */
+/* Per channel: symbol bits -> impulses +-amp every sps samples (a set bit sends -amp, bpsk.cxx:150) ->
+   pulse shaping with `taps` (the reference runs blkconv(RRC_TAPS_111, 111, 2048), bpsk.cxx:56-59,125,162) ->
+   float samples (what the reference writes into ring_buffer<float>, bpsk.cxx:164) or, fused, the 10-bit DAC
+   words of convert_samples_to_bytes (bpsk.cxx:76-101).  The waveform is the causal convolution from zero
+   state and continues across calls. */
+enum { SFE_TX_F32 = 0, SFE_TX_DAC10 = 1 };
+typedef struct sfe_bpsk_tx sfe_bpsk_tx;
+sfe_bpsk_tx *sfe_bpsk_tx_create(const float *taps, int n_taps, int sps, float amp, int n_channels);
+void sfe_bpsk_tx_destroy(sfe_bpsk_tx *t);
+int sfe_bpsk_tx_reset(sfe_bpsk_tx *t);
+/* d_bits: n_channels rows of packed symbols, bit j of word w = symbol 32 w + j (the reference consumes
+   rand() words LSB first, bpsk.cxx:148-150); row pitch in 32-bit words.  n_sym symbols per channel; for
+   SFE_TX_DAC10, n_sym * sps must be a multiple of 4.  Output rows: n_sym * sps floats, or n_sym * sps / 4 * 5
+   bytes; out_pitch in BYTES.  Enqueues on `stream`, returns without synchronising. */
+int sfe_bpsk_tx_process_dev(sfe_bpsk_tx *t, const uint32_t *d_bits, long n_sym, long pitch_words, void *d_out,
+                            long out_pitch, int out_fmt, void *stream);
+
 /* ---- sample format helpers (device wire formats) ---------------------- */
 /* float -> 10-bit DAC words, 4 samples -> 5 bytes: examples/bpsk/bpsk.cxx:76-101,
    gr-simplefe/lib/sink_c_impl.cc:118-144.  n must be a multiple of 4; device pointers. */

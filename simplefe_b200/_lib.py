@@ -63,6 +63,10 @@ SYMBOLS = {
     "sfe_chain_profile_enable": (_ci, [_vp, _ci]),
     "sfe_chain_profile_read": (_ci, [_vp, _ci, C.POINTER(C.c_float), C.POINTER(_ci)]),
     "sfe_pack_dac10_dev": (_ci, [_vp, _cl, _vp, _vp]),
+    "sfe_bpsk_tx_create": (_vp, [_f32p, _ci, _ci, _cf, _ci]),
+    "sfe_bpsk_tx_destroy": (None, [_vp]),
+    "sfe_bpsk_tx_reset": (_ci, [_vp]),
+    "sfe_bpsk_tx_process_dev": (_ci, [_vp, _vp, _cl, _cl, _vp, _cl, _ci, _vp]),
     "sfe_ring_create": (_vp, [_ci, _ci]),
     "sfe_ring_alloc": (_ci, [_vp, _ci]),
     "sfe_ring_destroy": (None, [_vp]),

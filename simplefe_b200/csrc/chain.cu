@@ -148,7 +148,10 @@ bool alloc_hist(Op &op, int S)
 {
     const size_t bytes = (size_t)S * op.H * fmt_bytes(op.in_fmt);
     for (int i = 0; i < 2; i++)
-        if (!SFE_CUDA(cudaMalloc(&op.hist[i], bytes ? bytes : 1)) || !SFE_CUDA(cudaMemset(op.hist[i], 0, bytes))) return false;
+        // zero state: offset-binary bytes encode 0.0 as 128 (source_c_impl.cc:126-129)
+        if (!SFE_CUDA(cudaMalloc(&op.hist[i], bytes ? bytes : 1)) ||
+            !SFE_CUDA(cudaMemset(op.hist[i], op.in_fmt == SFE_IN_U8 ? 0x80 : 0, bytes)))
+            return false;
     return true;
 }
 
@@ -586,7 +589,7 @@ extern "C" int sfe_chain_reset(sfe_chain *c)
         op.pre_ws = WalkState{};
         const size_t bytes = (size_t)c->S * op.H * fmt_bytes(op.in_fmt);
         for (int i = 0; i < 2; i++)
-            if (!SFE_CUDA(cudaMemset(op.hist[i], 0, bytes))) return SFE_ERR_CUDA;
+            if (!SFE_CUDA(cudaMemset(op.hist[i], op.in_fmt == SFE_IN_U8 ? 0x80 : 0, bytes))) return SFE_ERR_CUDA;
     }
     return SFE_OK;
 }

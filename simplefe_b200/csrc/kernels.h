@@ -108,6 +108,12 @@ size_t bank_smem_bytes(int n_rows, int row_len);
 int bank_max_live();
 int launch_bank(const BankParams &p, cudaStream_t st);
 
+// ---- batched BPSK transmit: bits -> RRC-shaped samples -> float or 10-bit DAC words (bpsk_tx_kernel.cu) ----
+int bpsk_tx_max_taps(int sps);
+int launch_bpsk_tx(const uint32_t *bits, long pitch_words, const uint64_t *hist_old, uint64_t *hist_new, int n_hist, long n_sym, int sps,
+                   const float *taps, int n_taps, float amp, int n_channels, int out_dac10, void *out, long out_pitch_bytes,
+                   cudaStream_t st);
+
 // ---- small utilities (util_kernels.cu) -----------------------------------------------------------
 // hist_new[s][0..H) <- last H samples of (hist_old ++ cur[0..n)) for every stream row; elem = bytes per sample
 int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long pitch, long n, int H, int elem, int n_streams,

@@ -343,3 +343,20 @@ def test_chain_bank_unaligned_device_rows(gpu_lib):
     torch.cuda.synchronize()
     got = d_out.cpu().numpy()[:, :n].view(np.complex64)[..., 0]
     assert np.array_equal(got, want)
+
+
+# ---- device wire format: u8 offset-binary I/Q (gr-simplefe/lib/source_c_impl.cc:121-132) ---------------
+
+@pytest.mark.parametrize("base", ["cfg5_small", "cfg2_small", "cfg4_small"])
+def test_chain_u8_wire_format_vs_oracle(gpu_lib, oracle_lib, base):
+    """the bytes the board sends, (b-128)*(1/127) fused into the first kernel's load"""
+    from oracle import oracle as O
+    from simplefe_b200.chain import Chain
+    cfg = dict(F.CONFIGS[base], in_fmt=F.IN_U8, S=5, N=40003)
+    iq = F.make_input(cfg)
+    assert iq.dtype == np.uint8
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib)
+    got = Chain(cfg["S"], cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b")).process(iq)
+    assert got.shape == ref.shape
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
