@@ -189,6 +189,22 @@ int sfe_bpsk_tx_reset(sfe_bpsk_tx *t);
 int sfe_bpsk_tx_process_dev(sfe_bpsk_tx *t, const uint32_t *d_bits, long n_sym, long pitch_words, void *d_out,
                             long out_pitch, int out_fmt, void *stream);
 
+/* ---- (5) streaming front door: device callback -> pinned ring -> GPU chain (additive) --------------------- */
+/* sfe_rx_feed_callback has the signature of libsimpleFE's sfe_callback (libsimpleFE/simpleFE.h:42) and the
+   behaviour of gr-simplefe's rx path (gr-simplefe/lib/source_c_impl.cc:84-108): pass it, with the feed as
+   userdata, to sfe_rx_start (simpleFE.h:59-62).  Odd-length packets are discarded with the reference's message,
+   a full ring prints "O" on stderr and drops the packet.  The chain must be one stream of SFE_IN_U8. */
+typedef struct sfe_rx_feed sfe_rx_feed;
+sfe_rx_feed *sfe_rx_feed_create(const sfe_chain_desc *desc, int ring_bytes, int block_samples);
+void sfe_rx_feed_destroy(sfe_rx_feed *f);
+int sfe_rx_feed_callback(unsigned char *buffer, int length, void *feed);
+/* consumer side (the role of source_c_impl::work, source_c_impl.cc:134-153): runs every whole block that is
+   buffered through the chain and appends the complex64 outputs to `out` (host memory, cap in samples); waits
+   up to wait_ms for the first block.  Returns the number of output samples, or a negative status. */
+long sfe_rx_feed_pump(sfe_rx_feed *f, void *out, long cap, int wait_ms);
+/* which: 0 overflows ("O"), 1 discarded odd packets, 2 bytes accepted, 3 bytes waiting in the ring */
+long sfe_rx_feed_stat(sfe_rx_feed *f, int which);
+
 /* ---- sample format helpers (device wire formats) ---------------------- */
 /* float -> 10-bit DAC words, 4 samples -> 5 bytes: examples/bpsk/bpsk.cxx:76-101,
    gr-simplefe/lib/sink_c_impl.cc:118-144.  n must be a multiple of 4; device pointers. */

@@ -67,6 +67,11 @@ SYMBOLS = {
     "sfe_bpsk_tx_destroy": (None, [_vp]),
     "sfe_bpsk_tx_reset": (_ci, [_vp]),
     "sfe_bpsk_tx_process_dev": (_ci, [_vp, _vp, _cl, _cl, _vp, _cl, _ci, _vp]),
+    "sfe_rx_feed_create": (_vp, [C.POINTER(ChainDesc), _ci, _ci]),
+    "sfe_rx_feed_destroy": (None, [_vp]),
+    "sfe_rx_feed_callback": (_ci, [_vp, _ci, _vp]),
+    "sfe_rx_feed_pump": (_cl, [_vp, _vp, _cl, _ci]),
+    "sfe_rx_feed_stat": (_cl, [_vp, _ci]),
     "sfe_ring_create": (_vp, [_ci, _ci]),
     "sfe_ring_alloc": (_ci, [_vp, _ci]),
     "sfe_ring_destroy": (None, [_vp]),

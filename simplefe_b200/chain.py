@@ -19,27 +19,63 @@ def stage(klass: int, taps, up: int, blk: int, rate: float) -> dict:
     return dict(klass=klass, taps=taps, up=up, blk=blk, rate=rate)
 
 
+def make_desc(n_streams: int, in_fmt: int, blkconv=None, stage_a=None, stage_b=None, flags: int = 0):
+    """(sfe_chain_desc, keep-alive list of the tap arrays it points to)"""
+    d = ChainDesc()
+    d.in_fmt, d.n_streams, d.flags = int(in_fmt), int(n_streams), int(flags)
+    keep = []
+    if blkconv is not None:
+        t = np.ascontiguousarray(np.asarray(blkconv[0], np.float32))
+        keep.append(t)
+        d.bc_taps, d.bc_ntaps, d.bc_fft = t.ctypes.data_as(_f32p), len(t), int(blkconv[1])
+    for name, st in (("a", stage_a), ("b", stage_b)):
+        if st is None:
+            continue
+        t = np.ascontiguousarray(np.asarray(st["taps"], np.float32))
+        keep.append(t)
+        s = getattr(d, name)
+        s.klass, s.taps, s.n_taps = int(st["klass"]), t.ctypes.data_as(_f32p), len(t)
+        s.up, s.blk, s.rate = int(st["up"]), int(st["blk"]), float(st["rate"])
+    return d, keep
+
+
+class RxFeed:
+    """Streaming front door (sfe_rx_feed_*): device callback -> pinned ring -> GPU chain."""
+
+    def __init__(self, ring_bytes: int, block_samples: int, blkconv=None, stage_a=None, stage_b=None, flags: int = 0):
+        self._l = lib()
+        d, keep = make_desc(1, IN_U8, blkconv, stage_a, stage_b, flags)
+        self._h = self._l.sfe_rx_feed_create(C.byref(d), int(ring_bytes), int(block_samples))
+        if not self._h:
+            raise SfeError(f"sfe_rx_feed_create: {last_error()}")
+
+    def callback(self, packet: bytes) -> int:
+        """what the USB thread does: sfe_rx_feed_callback(buffer, length, feed)"""
+        buf = (C.c_ubyte * len(packet)).from_buffer_copy(packet)
+        return self._l.sfe_rx_feed_callback(C.addressof(buf), len(packet), self._h)
+
+    def pump(self, cap: int, wait_ms: int = 0) -> np.ndarray:
+        out = np.zeros(int(cap), np.complex64)
+        n = self._l.sfe_rx_feed_pump(self._h, out.ctypes.data, int(cap), int(wait_ms))
+        check(int(n), "sfe_rx_feed_pump")
+        return out[:n]
+
+    def stat(self, which: int) -> int:
+        return int(self._l.sfe_rx_feed_stat(self._h, int(which)))
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._l.sfe_rx_feed_destroy(h)
+
+
 class Chain:
     def __init__(self, n_streams: int, in_fmt: int = IN_I16, blkconv=None, stage_a=None, stage_b=None, flags: int = 0,
                  device: int | None = None):
         self._l = lib()
         if device is not None:
             check(self._l.sfe_set_device(int(device)), "sfe_set_device")
-        d = ChainDesc()
-        d.in_fmt, d.n_streams, d.flags = int(in_fmt), int(n_streams), int(flags)
-        keep = []
-        if blkconv is not None:
-            t = np.ascontiguousarray(np.asarray(blkconv[0], np.float32))
-            keep.append(t)
-            d.bc_taps, d.bc_ntaps, d.bc_fft = t.ctypes.data_as(_f32p), len(t), int(blkconv[1])
-        for name, st in (("a", stage_a), ("b", stage_b)):
-            if st is None:
-                continue
-            t = np.ascontiguousarray(np.asarray(st["taps"], np.float32))
-            keep.append(t)
-            s = getattr(d, name)
-            s.klass, s.taps, s.n_taps = int(st["klass"]), t.ctypes.data_as(_f32p), len(t)
-            s.up, s.blk, s.rate = int(st["up"]), int(st["blk"]), float(st["rate"])
+        d, keep = make_desc(n_streams, in_fmt, blkconv, stage_a, stage_b, flags)
         self._h = self._l.sfe_chain_create(C.byref(d))
         if not self._h:
             raise SfeError(f"sfe_chain_create: {last_error()}")
