@@ -41,6 +41,13 @@ def run_case(name, cfg, S, N, flags, steps, warmup, peak, torch, Chain):
             blk = torch.randn((min(rows, S - s0), N, 2), generator=g, device=dev) * 0.25
             d_in[s0:s0 + rows] = torch.round(blk.clamp_(-1, 1) * 32767.0).to(torch.int16)
         del blk
+    elif cfg["in_fmt"] == F.IN_U8:
+        d_in = torch.empty((S, N, 2), dtype=torch.uint8, device=dev)
+        rows = max(1, (128 << 20) // (N * 8))
+        for s0 in range(0, S, rows):
+            blk = torch.randn((min(rows, S - s0), N, 2), generator=g, device=dev) * 0.25
+            d_in[s0:s0 + rows] = (torch.round(blk.clamp_(-1, 1) * 127.0) + 128).clamp_(0, 255).to(torch.uint8)
+        del blk
     else:
         d_in = (torch.randn((S, N, 2), generator=g, device=dev) * 0.25).clamp_(-1, 1)
     ch = Chain(S, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), flags=flags, device=0)
@@ -102,6 +109,7 @@ def main():
         ("cfg4 bpsk chain, fractional rates (single stream)", C["cfg4"], 1, 1_000_000, 0),
         ("cfg4 bpsk chain, fractional rates x256 streams", C["cfg4"], 256, 1_000_000, 0),
         ("cfg5 chain x1024 [one fused bank kernel]", C["cfg5"], 1024, big, 0),
+        ("cfg5 chain x1024, u8 device wire format [one fused bank kernel]", dict(C["cfg5"], in_fmt=F.IN_U8), 1024, big, 0),
         ("cfg5 chain x1024 [fused blkconv*decim on tcgen05 + generic resample]", C["cfg5"], 1024, big, FLAG_NO_BANK),
         ("cfg5 chain x1024 [fused blkconv*decim CUDA-core FIR + generic]", C["cfg5"], 1024, big, FLAG_NO_BANK | FLAG_NO_TENSOR),
         ("cfg5 chain x256 [stage by stage: FFT blkconv, FIR, generic]", C["cfg5"], 256, big, FLAG_NO_BANK | FLAG_NO_FUSE | FLAG_NO_TENSOR),

@@ -293,21 +293,24 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
                 return SFE_ERR_ARG;
             }
             // TMA needs 16-byte aligned rows: realign caller buffers that are not
-            if ((reinterpret_cast<uintptr_t>(src) & 15) || (src_pitch & 3)) {
-                const long ap = (op.n_in + 3) & ~3L;
-                if (!ensure(&w.d_align, &w.align_bytes, (size_t)ns * ap * 4)) return SFE_ERR_CUDA;
-                if (!SFE_CUDA(cudaMemcpy2DAsync(w.d_align, (size_t)ap * 4, src, (size_t)src_pitch * 4, (size_t)op.n_in * 4, ns,
+            if ((reinterpret_cast<uintptr_t>(src) & 15) || ((src_pitch * eb) & 15)) {
+                const long ap = (op.n_in + 7) & ~7L;                     // 16-byte rows in either format
+                if (!ensure(&w.d_align, &w.align_bytes, (size_t)ns * ap * eb)) return SFE_ERR_CUDA;
+                if (!SFE_CUDA(cudaMemcpy2DAsync(w.d_align, (size_t)ap * eb, src, (size_t)src_pitch * eb, (size_t)op.n_in * eb, ns,
                                                 cudaMemcpyDeviceToDevice, st)))
                     return SFE_ERR_CUDA;
                 in.cur = w.d_align;
                 in.pitch = ap;
             }
-            const int key = op.rows_per_phase == 4 ? -1 : (int)(op.n_first & 3);
+            const int spc = 16 / eb;                                     // samples per 16-byte chunk
+            const int key = op.rows_per_phase > 1 ? -1 : (int)(((op.n_first % spc) + spc) % spc);
             auto it = op.d_tables.find(key);
             if (it == op.d_tables.end()) {
                 std::vector<float> rows;
                 int rl = 0, nr = 0, tc = 0;
-                bank_table(op.g, op.D, op.r, op.up, (double)(1.0f / 32767.0f), key, rows, &rl, &nr, &tc);
+                // the sample scale of the format (SURVEY.md D2 / source_c_impl.cc:126) lives in the taps
+                const double scale = op.in_fmt == SFE_IN_U8 ? (double)(1.0f / 127.0f) : (double)(1.0f / 32767.0f);
+                bank_table(op.g, op.D, op.r, op.up, scale, key, spc, rows, &rl, &nr, &tc);
                 float *d = nullptr;
                 if (!upload(&d, rows)) return SFE_ERR_CUDA;
                 it = op.d_tables.emplace(key, d).first;
@@ -429,7 +432,7 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
     // needs: int16 input, a last stage with an integral multi-phase step, and before it nothing but FIRs that
     // keep every D-th sample (blkconv and/or an integral decimator).  Everything else uses the staged plans.
     bool bank = false;
-    if (!(d->flags & (SFE_FLAG_EXACT | SFE_FLAG_NO_BANK)) && d->in_fmt == SFE_IN_I16 && has_a && (!has_b || a_decim)) {
+    if (!(d->flags & (SFE_FLAG_EXACT | SFE_FLAG_NO_BANK)) && (d->in_fmt == SFE_IN_I16 || d->in_fmt == SFE_IN_U8) && has_a && (!has_b || a_decim)) {
         const sfe_stage_desc &bs = has_b ? d->b : d->a;
         long step_b = 0;
         if (integral_step(bs, &step_b) && step_b % bs.up != 0) {
@@ -461,18 +464,19 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
             }
             const int J = ((int)op.r.size() + op.up - 1) / op.up;
             const int Tc = op.D * (J - 1) + (int)op.g.size();
-            const int NC = bank_nc(Tc);
+            const int spc = 16 / fmt_bytes(fmt), box = 8 * spc;          // samples per 16-byte chunk / per 128-byte box row
+            const int NC = bank_nc(Tc, spc);
             op.nc = NC;
-            op.row_len = bank_row_len(Tc);
-            op.rows_per_phase = op.D % 4 == 0 ? 1 : 4;
+            op.row_len = bank_row_len(Tc, spc);
+            op.rows_per_phase = op.D % spc == 0 ? 1 : spc;
             op.n_rows = op.up * op.rows_per_phase;
             const long spacing = (long)op.D * (step_b / op.up);          // samples between consecutive outputs, at least
-            // windows open and close on 32-sample box boundaries: at most one may open per box, and a box is
-            // overlapped by the windows whose first chunk lies in a range of NC + 7 chunks
-            const long live = spacing >= 64 ? (NC + 6) / (spacing / 4) + 1 : 1 << 30;
+            // windows open and close on box boundaries: at most one may open per box, and a box is overlapped by
+            // the windows whose first chunk lies in a range of NC + 7 chunks
+            const long live = spacing >= 2 * box ? (NC + 6) / (spacing / spc) + 1 : 1 << 30;
             if (live <= bank_max_live() && bank_smem_bytes(op.n_rows, op.row_len) <= 227 * 1024) {
                 op.n_live = (int)live;
-                op.H = (4 * NC + 2 * op.D + 4 + 31) / 32 * 32;
+                op.H = (spc * NC + 2 * op.D + spc + box - 1) / box * box;
                 op.name = std::string("bank_fused(") + (has_bc ? "blkconv*" : "") + (has_b ? "decim*" : "") + "polyphase)/L" +
                           std::to_string(op.up) + "D" + std::to_string(op.D) + "T" + std::to_string(Tc);
                 c->plan = op.name;

@@ -31,8 +31,8 @@ namespace sfe {
 
 namespace {
 
-constexpr int BOX_SAMPLES = 32, BOX_ROWS = 32;
-constexpr int BOX_BYTES = BOX_SAMPLES * BOX_ROWS * 4;   // one TMA box = one ring slot = 8 chunks of 4 samples per lane
+constexpr int BOX_SAMPLES = 32, BOX_ROWS = 32;          // a box row is 32 words = 128 bytes: 32 int16 or 64 u8 complex samples
+constexpr int BOX_BYTES = BOX_SAMPLES * BOX_ROWS * 4;   // one TMA box = 8 chunks of 16 bytes per lane
 constexpr int SLOT_BOXES = 2;         // boxes (time blocks of 128 B per row) fetched by one TMA instruction
 constexpr int SLOT_BYTES = SLOT_BOXES * BOX_BYTES;
 constexpr int A_MAX = 4;             // window slots per lane, at most
@@ -156,22 +156,72 @@ __device__ __forceinline__ void convert4(const uint4 &w, f32x2 &i01, f32x2 &i23,
     }
 }
 
-// one chunk (4 samples of this lane's stream) into the NA window slots.  Accumulators hold (even, odd) partial
-// sums: the pair of consecutive samples meets the pair of consecutive taps in one FFMA2.
+// ---- u8 offset-binary I/Q -> float, eight complex samples per 128-bit word (bytes I0 Q0 I1 Q1 per 32 bits) ----
+// The value is b - 128 (gr-simplefe/lib/source_c_impl.cc:126-129; the 1/127 lives in the taps), exact in float.
+// CONV 10: exponent trick: bits 0x4B00_0000 | b are the float 8388608 + b, a packed FADD2 subtracts 8388736;
+// 11: xor 0x80 makes the byte a signed b - 128, I2F.S8 with a byte selector converts it (XU pipe);
+// 12: I through the XU, Q through the exponent trick.
+__device__ __forceinline__ float u8_magic(uint32_t w, int byte)
+{
+    const uint32_t K = 0x4B000000u;
+    return __uint_as_float(__byte_perm(w, K, 0x7650 + byte));      // (w.byte, K.b1, K.b2, K.b3)
+}
+__device__ __forceinline__ float s8_xu(uint32_t wx, int byte)     // wx = w ^ 0x80808080
+{
+    return (float)(signed char)((wx >> (8 * byte)) & 0xffu);
+}
+template <int CONV>
+__device__ __forceinline__ void convert_u8_pair(uint32_t wa, uint32_t wb, f32x2 &iA, f32x2 &qA, f32x2 &iB, f32x2 &qB)
+{
+    // wa holds samples (0,1), wb samples (2,3) of a group of four
+    const f32x2 off = pack2(-8388736.0f, -8388736.0f);
+    const bool ixu = CONV == 11 || CONV == 12, qxu = CONV == 11;
+    const uint32_t xa = wa ^ 0x80808080u, xb = wb ^ 0x80808080u;
+    iA = ixu ? pack2(s8_xu(xa, 0), s8_xu(xa, 2)) : fadd2(pack2(u8_magic(wa, 0), u8_magic(wa, 2)), off);
+    iB = ixu ? pack2(s8_xu(xb, 0), s8_xu(xb, 2)) : fadd2(pack2(u8_magic(wb, 0), u8_magic(wb, 2)), off);
+    qA = qxu ? pack2(s8_xu(xa, 1), s8_xu(xa, 3)) : fadd2(pack2(u8_magic(wa, 1), u8_magic(wa, 3)), off);
+    qB = qxu ? pack2(s8_xu(xb, 1), s8_xu(xb, 3)) : fadd2(pack2(u8_magic(wb, 1), u8_magic(wb, 3)), off);
+}
+
+__host__ __device__ constexpr int conv_spc(int conv) { return conv >= 10 ? 8 : 4; }   // samples per 16-byte chunk
+
+// one chunk (16 bytes of this lane's stream: 4 int16 or 8 u8 complex samples) into the NA window slots.
+// Accumulators hold (even, odd) partial sums: a pair of consecutive samples meets the pair of consecutive taps
+// in one FFMA2.  TOFF = byte offset of this chunk's taps from the slot's tap pointer.
 template <int NA, int CONV, int TOFF>
 __device__ __forceinline__ void chunk(uint32_t addr, f32x2 (&accI)[NA], f32x2 (&accQ)[NA], const uint32_t (&tp)[NA])
 {
     const uint4 w = lds_u4(addr);
-    f32x2 i01, i23, q01, q23;
-    convert4<CONV>(w, i01, i23, q01, q23);
+    if (conv_spc(CONV) == 4) {
+        f32x2 i01, i23, q01, q23;
+        convert4<CONV>(w, i01, i23, q01, q23);
 #pragma unroll
-    for (int j = 0; j < NA; j++) {
-        f32x2 t01, t23;
-        lds_taps<TOFF>(tp[j], t01, t23);
-        accI[j] = ffma2(i01, t01, accI[j]);
-        accQ[j] = ffma2(q01, t01, accQ[j]);
-        accI[j] = ffma2(i23, t23, accI[j]);
-        accQ[j] = ffma2(q23, t23, accQ[j]);
+        for (int j = 0; j < NA; j++) {
+            f32x2 t01, t23;
+            lds_taps<TOFF>(tp[j], t01, t23);
+            accI[j] = ffma2(i01, t01, accI[j]);
+            accQ[j] = ffma2(q01, t01, accQ[j]);
+            accI[j] = ffma2(i23, t23, accI[j]);
+            accQ[j] = ffma2(q23, t23, accQ[j]);
+        }
+    } else {
+        f32x2 i01, i23, i45, i67, q01, q23, q45, q67;
+        convert_u8_pair<CONV>(w.x, w.y, i01, q01, i23, q23);
+        convert_u8_pair<CONV>(w.z, w.w, i45, q45, i67, q67);
+#pragma unroll
+        for (int j = 0; j < NA; j++) {
+            f32x2 t01, t23, t45, t67;
+            lds_taps<TOFF>(tp[j], t01, t23);
+            lds_taps<TOFF + 16>(tp[j], t45, t67);
+            accI[j] = ffma2(i01, t01, accI[j]);
+            accQ[j] = ffma2(q01, t01, accQ[j]);
+            accI[j] = ffma2(i23, t23, accI[j]);
+            accQ[j] = ffma2(q23, t23, accQ[j]);
+            accI[j] = ffma2(i45, t45, accI[j]);
+            accQ[j] = ffma2(q45, t45, accQ[j]);
+            accI[j] = ffma2(i67, t67, accI[j]);
+            accQ[j] = ffma2(q67, t67, accQ[j]);
+        }
     }
 }
 
@@ -180,30 +230,32 @@ __device__ __forceinline__ void chunk(uint32_t addr, f32x2 (&accI)[NA], f32x2 (&
 template <int NA, int CONV>
 __device__ __forceinline__ void run_box(uint32_t ax, f32x2 (&accI)[NA], f32x2 (&accQ)[NA], uint32_t (&tp)[NA])
 {
-    chunk<NA, CONV, 0>(ax, accI, accQ, tp);
-    chunk<NA, CONV, 16>(ax ^ 0x10u, accI, accQ, tp);
-    chunk<NA, CONV, 32>(ax ^ 0x20u, accI, accQ, tp);
-    chunk<NA, CONV, 48>(ax ^ 0x30u, accI, accQ, tp);
-    chunk<NA, CONV, 64>(ax ^ 0x40u, accI, accQ, tp);
-    chunk<NA, CONV, 80>(ax ^ 0x50u, accI, accQ, tp);
-    chunk<NA, CONV, 96>(ax ^ 0x60u, accI, accQ, tp);
-    chunk<NA, CONV, 112>(ax ^ 0x70u, accI, accQ, tp);
+    constexpr int TB = conv_spc(CONV) * 4;     // tap bytes per chunk
+    chunk<NA, CONV, 0 * TB>(ax, accI, accQ, tp);
+    chunk<NA, CONV, 1 * TB>(ax ^ 0x10u, accI, accQ, tp);
+    chunk<NA, CONV, 2 * TB>(ax ^ 0x20u, accI, accQ, tp);
+    chunk<NA, CONV, 3 * TB>(ax ^ 0x30u, accI, accQ, tp);
+    chunk<NA, CONV, 4 * TB>(ax ^ 0x40u, accI, accQ, tp);
+    chunk<NA, CONV, 5 * TB>(ax ^ 0x50u, accI, accQ, tp);
+    chunk<NA, CONV, 6 * TB>(ax ^ 0x60u, accI, accQ, tp);
+    chunk<NA, CONV, 7 * TB>(ax ^ 0x70u, accI, accQ, tp);
 #pragma unroll
-    for (int j = 0; j < NA; j++) tp[j] += 128;
+    for (int j = 0; j < NA; j++) tp[j] += 8 * TB;
 }
 
 struct OutInfo {
-    int E;     // chunk (4 samples, counted from sample -H) that holds the newest sample of the window
+    int E;     // chunk (16 bytes, counted from sample -H) that holds the newest sample of the window
     int row;   // row of the bank table
 };
 
 // output at decimated index M, phase ph
+template <int SPC>
 __device__ __forceinline__ OutInfo out_info(const BankParams &p, long M, int ph)
 {
     const long rh = p.n_first + (long)p.D * M + p.H;      // newest sample, counted from sample -H
     OutInfo o;
-    o.E = (int)(rh >> 2);
-    o.row = p.rows_per_phase == 4 ? ph * 4 + (int)(rh & 3) : ph;
+    o.E = (int)(rh / SPC);
+    o.row = p.rows_per_phase > 1 ? ph * SPC + (int)(rh % SPC) : ph;
     return o;
 }
 __device__ __forceinline__ void split_pos(const BankParams &p, long k, long &M, int &ph)
@@ -248,27 +300,28 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     const int g = (int)(item % p.n_groups), seg = (int)(item / p.n_groups);
     const long k_lo = p.n_out * seg / p.n_seg, k_hi = p.n_out * (seg + 1) / p.n_seg;
     if (k_lo >= k_hi) return;
+    constexpr int SPC = conv_spc(CONV);             // samples per 16-byte chunk
     const int NC = p.nc;
     const int row_bytes = p.row_len * 4;
 
     long M_next;
     int ph_next;
     split_pos(p, k_lo, M_next, ph_next);
-    const OutInfo first = out_info(p, M_next, ph_next);
+    const OutInfo first = out_info<SPC>(p, M_next, ph_next);
     OutInfo last;
     {
         long Ml;
         int phl;
         split_pos(p, k_hi - 1, Ml, phl);
-        last = out_info(p, Ml, phl);
+        last = out_info<SPC>(p, Ml, phl);
     }
     const int q_begin = first.E - NC + 1, q_end = last.E;          // chunks this item reads (inclusive)
     const int box0 = q_begin >> 3;                                 // 8 chunks per box
     const int n_boxes = (q_end >> 3) - box0 + 1;
     const int slot0 = box0 >> 1;                                   // slots pair boxes (2a, 2a+1) of the absolute box grid
     const int n_slots = (q_end >> 4) - slot0 + 1;
-    const int hist_boxes = p.H >> 5;
-    const int full_tb = (int)(p.in.n >> 5);                        // whole 128-byte time blocks of the current rows
+    const int hist_boxes = p.H / (8 * SPC);                        // a box = 128 bytes = 8 chunks per row
+    const int full_tb = (int)(p.in.n / (8 * SPC));                 // whole 128-byte time blocks of the current rows
     const uint32_t bar0 = smem_u32(&bars[warp * NST]);
 
     // A slot whose two boxes are whole blocks of the same buffer comes in as ONE 3-D box (32 samples, 2 blocks, 32 rows):
@@ -329,7 +382,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
         if (bi == 0 || tb == 0) mbar_wait(bar0 + 8 * slot, phase);   // first box of a slot
         if (B == open_box) {                                         // a window opens in this box (at most one)
             const int S = nxt.E - NC + 1;                            // its first chunk
-            const uint32_t t0 = table_a + (uint32_t)(nxt.row * row_bytes) + (uint32_t)(PAD_CHUNKS - (S & 7)) * 16u;
+            const uint32_t t0 = table_a + (uint32_t)(nxt.row * row_bytes) + (uint32_t)(PAD_CHUNKS - (S & 7)) * (uint32_t)(SPC * 4);
 #pragma unroll
             for (int j = 0; j < NLIVE; j++)
                 if (j == nact) {
@@ -343,7 +396,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
                 ph_next += sP;
                 M_next += sM;
                 if (ph_next >= p.L) { ph_next -= p.L; M_next += 1; }
-                nxt = out_info(p, M_next, ph_next);
+                nxt = out_info<SPC>(p, M_next, ph_next);
                 open_box = (nxt.E - NC + 1) >> 3;
             } else {
                 open_box = 0x3fffffff;
@@ -442,17 +495,17 @@ bool encode_rows3(CUtensorMap *m, const void *base, long n_blocks, long n_rows, 
 
 // ---- launch variants: warps per CTA, ring slots per warp, conversion flavour ----------------------------------
 struct BankVariant {
-    int warps, nst, conv;
+    int warps, nst, conv, conv8;   // conv: int16 flavour (0-3), conv8: u8 flavour (10-12)
 };
 typedef void (*BankKernel)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const BankParams);
 
 BankVariant bank_variant()
 {
     static BankVariant v = [] {
-        BankVariant d{8, 2, 2};
-        if (const char *e = getenv("SFE_BANK_VARIANT")) {   // tuning hook: "warps,slots,conv"
-            int w = 0, n = 0, c = 0;
-            if (sscanf(e, "%d,%d,%d", &w, &n, &c) == 3) d = BankVariant{w, n, c};
+        BankVariant d{8, 2, 2, 12};
+        if (const char *e = getenv("SFE_BANK_VARIANT")) {   // tuning hook: "warps,slots,conv[,conv8]"
+            int w = 0, n = 0, c = 0, c8 = 12;
+            if (sscanf(e, "%d,%d,%d,%d", &w, &n, &c, &c8) >= 3) d = BankVariant{w, n, c, c8};
         }
         return d;
     }();
@@ -471,8 +524,17 @@ BankKernel bank_pick_live(int live)
     }
 }
 
-BankKernel bank_pick(const BankVariant &v, int live)
+BankKernel bank_pick(const BankVariant &v, int live, int fmt)
 {
+    if (fmt == SFE_IN_U8) {
+        switch (v.warps * 100 + v.conv8) {
+            case 810: return bank_pick_live<8, 2, 10>(live);
+            case 811: return bank_pick_live<8, 2, 11>(live);
+            case 812: return bank_pick_live<8, 2, 12>(live);
+            case 1012: return bank_pick_live<10, 2, 12>(live);
+            default: return nullptr;
+        }
+    }
     const int key = v.warps * 100 + v.nst * 10 + v.conv;
     switch (key) {
         case 820: return bank_pick_live<8, 2, 0>(live);
@@ -494,27 +556,32 @@ size_t bank_smem_bytes(int n_rows, int row_len)
 }
 
 int bank_max_live() { return A_MAX; }
-int bank_nc(int Tc) { return (Tc + 6) / 4; }
-int bank_row_len(int Tc) { return 4 * (bank_nc(Tc) + 2 * PAD_CHUNKS); }
+int bank_nc(int Tc, int spc) { return (Tc + 2 * spc - 2) / spc; }
+int bank_row_len(int Tc, int spc) { return spc * (bank_nc(Tc, spc) + 2 * PAD_CHUNKS); }
 
 int launch_bank(const BankParams &p_in, cudaStream_t st)
 {
     BankParams p = p_in;
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
-    if ((reinterpret_cast<uintptr_t>(p.in.cur) & 15) || (p.in.pitch & 3) || (p.H & 31) || p.in.fmt != SFE_IN_I16) {
-        set_error("fused bank: input rows must be int16 IQ, 16-byte aligned with a pitch that is a multiple of 4 samples");
+    const int eb = fmt_bytes(p.in.fmt);                      // bytes per complex sample: 4 (int16) or 2 (u8)
+    const int spc = 16 / eb;
+    if ((reinterpret_cast<uintptr_t>(p.in.cur) & 15) || ((p.in.pitch * eb) & 15) || (p.H % (8 * spc)) ||
+        (p.in.fmt != SFE_IN_I16 && p.in.fmt != SFE_IN_U8)) {
+        set_error("fused bank: input rows must be int16 or u8 IQ, 16-byte aligned with a pitch that is a multiple of 16 bytes");
         return SFE_ERR_ARG;
     }
     const BankVariant v = bank_variant();
-    BankKernel kern = bank_pick(v, p.n_live);
+    BankKernel kern = bank_pick(v, p.n_live, p.in.fmt);
     if (!kern) {
         set_error("fused bank: SFE_BANK_VARIANT names a variant that is not compiled in (or n_live is out of range)");
         return SFE_ERR_ARG;
     }
     CUtensorMap mc, mh, mc3, mh3;
-    if (!encode_rows(&mc, p.in.cur, p.in.n, p.n_streams, p.in.pitch) || !encode_rows(&mh, p.in.hist, p.H, p.n_streams, p.H) ||
-        !encode_rows3(&mc3, p.in.cur, p.in.n / BOX_SAMPLES, p.n_streams, p.in.pitch) ||
-        !encode_rows3(&mh3, p.in.hist, p.H / BOX_SAMPLES, p.n_streams, p.H))
+    // tensor maps count 32-bit words: one int16 sample or two u8 samples
+    const long n_words = (p.in.n * eb + 3) / 4, pitch_words = p.in.pitch * eb / 4, hist_words = (long)p.H * eb / 4;
+    if (!encode_rows(&mc, p.in.cur, n_words, p.n_streams, pitch_words) || !encode_rows(&mh, p.in.hist, hist_words, p.n_streams, hist_words) ||
+        !encode_rows3(&mc3, p.in.cur, p.in.n * eb / (BOX_SAMPLES * 4), p.n_streams, pitch_words) ||
+        !encode_rows3(&mh3, p.in.hist, hist_words / BOX_SAMPLES, p.n_streams, hist_words))
         return SFE_ERR_CUDA;
     int dev = 0, sms = 0;
     if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
@@ -534,16 +601,16 @@ int launch_bank(const BankParams &p_in, cudaStream_t st)
 }
 
 // Host side: the bank table.  c_ph[u] = sum_j r[ph + L j] g[u - D j] in double, scaled, rounded to float, stored
-// time-reversed and chunk aligned: row (ph, e) holds, for chunk-relative sample i, the tap u = 4 NC - 4 + e - i
-// where e = (newest sample + H) mod 4.
-void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r, int L, double scale, int e_only,
+// time-reversed and chunk aligned (spc samples per 16-byte chunk): row (ph, e) holds, behind PAD_CHUNKS zero
+// chunks, for chunk-relative sample i the tap u = spc NC - spc + e - i, where e = (newest sample + H) mod spc.
+void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r, int L, double scale, int e_only, int spc,
                 std::vector<float> &rows, int *row_len, int *n_rows, int *Tc_out)
 {
     const int J = ((int)r.size() + L - 1) / L;
     const int Tc = D * (J - 1) + (int)g.size();
-    const int NC = bank_nc(Tc);
-    const int RL = bank_row_len(Tc);              // zero pads: windows open and close on box boundaries (kernel)
-    const int per = e_only >= 0 ? 1 : 4;
+    const int NC = bank_nc(Tc, spc);
+    const int RL = bank_row_len(Tc, spc);         // zero pads: windows open and close on box boundaries (kernel)
+    const int per = e_only >= 0 ? 1 : spc;
     rows.assign((size_t)L * per * RL, 0.f);
     std::vector<double> c((size_t)Tc);
     for (int ph = 0; ph < L; ph++) {
@@ -556,9 +623,9 @@ void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r
         for (int v = 0; v < per; v++) {
             const int e = e_only >= 0 ? e_only : v;
             float *row = rows.data() + ((size_t)ph * per + v) * RL;
-            for (int i = 0; i < 4 * NC; i++) {
-                const int u = 4 * NC - 4 + e - i;
-                if (u >= 0 && u < Tc) row[4 * PAD_CHUNKS + i] = (float)(c[u] * scale);
+            for (int i = 0; i < spc * NC; i++) {
+                const int u = spc * NC - spc + e - i;
+                if (u >= 0 && u < Tc) row[spc * PAD_CHUNKS + i] = (float)(c[u] * scale);
             }
         }
     }

@@ -83,7 +83,7 @@ int launch_toeplitz(const ToepParams &p, cudaStream_t st);
 // ---- K3: fused polyphase bank over many int16 IQ streams (fused_bank_kernel.cu) ------------------
 // y[k] = sum_u c_ph[u] x[R_k - u];  pos = pos0 + k*step, M = floor(pos/L), ph = pos mod L, R_k = n_first + D*M
 struct BankParams {
-    StreamView in;        // int16 IQ rows, 16-byte aligned, pitch % 4 == 0; history of H samples
+    StreamView in;        // int16 or u8 IQ rows, 16-byte aligned, pitch a multiple of 16 bytes; history of H samples
     float2 *out;
     long out_pitch;
     int n_streams;
@@ -91,18 +91,18 @@ struct BankParams {
     long pos0, step;      // output schedule on the L-times upsampled grid of the (virtual) decimated stream
     int L, D;
     long n_first;         // raw index of decimated sample 0 of this call
-    int H;                // history depth in samples, multiple of 32
+    int H;                // history depth in samples, multiple of 128 bytes
     const float *table;   // device: n_rows rows of row_len floats (bank_table)
     int row_len, n_rows;  // row_len = 4 * (nc + 2 * pad chunks): bank_row_len()
     int nc;               // chunks (4 samples) of taps per row
     int n_live;           // window slots per lane: the most windows that ever overlap one 32-sample box
-    int rows_per_phase;   // 1: one alignment per call (D % 4 == 0), 4: row = ph*4 + alignment
+    int rows_per_phase;   // 1: one alignment per call (D % spc == 0), spc: row = ph*spc + alignment
     // filled by launch_bank
     int n_groups, n_seg;
 };
-int bank_nc(int Tc);                  // chunks of taps for a composite filter of Tc taps (any alignment)
-int bank_row_len(int Tc);             // floats per table row, zero pads included
-void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r, int L, double scale, int e_only,
+int bank_nc(int Tc, int spc);         // 16-byte chunks (spc samples each) of taps for a composite filter of Tc taps
+int bank_row_len(int Tc, int spc);    // floats per table row, zero pads included
+void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r, int L, double scale, int e_only, int spc,
                 std::vector<float> &rows, int *row_len, int *n_rows, int *Tc);
 size_t bank_smem_bytes(int n_rows, int row_len);
 int bank_max_live();

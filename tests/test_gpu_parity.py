@@ -360,3 +360,28 @@ def test_chain_u8_wire_format_vs_oracle(gpu_lib, oracle_lib, base):
     assert got.shape == ref.shape
     nrms, peak = F.err_metrics(got, ref)
     assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
+
+
+@pytest.mark.parametrize("S,N,splits", [(33, 70001, (1, 4097, 30000, 30001, 70001)), (2, 9001, (64, 65, 4000, 9001))])
+def test_chain_u8_bank_chunk_invariance(gpu_lib, oracle_lib, S, N, splits):
+    """u8 rows through the fused bank kernel (8 samples per 16-byte chunk): any split of the stream into calls
+    gives the same samples, and they match the reference classes"""
+    from oracle import oracle as O
+    from simplefe_b200.chain import Chain
+    cfg = dict(F.CONFIGS["cfg5_small"], in_fmt=F.IN_U8, S=S, N=N)
+    iq = F.make_input(cfg)
+    ch = Chain(S, F.IN_U8, cfg["blkconv"], cfg["stage_a"], cfg["stage_b"])
+    assert ch.plan.startswith("bank_fused")
+    whole = ch.process(iq)
+    ch.reset()
+    parts, a = [], 0
+    for b in splits:
+        parts.append(ch.process(iq[:, a:b]))
+        a = b
+    pieces = np.concatenate(parts, axis=1)
+    assert pieces.shape == whole.shape
+    nrms, peak = F.err_metrics(pieces, whole)
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
+    ref, _ = O.chain_run(iq, F.IN_U8, cfg["blkconv"], cfg["stage_a"], cfg["stage_b"], lib=oracle_lib)
+    nrms, peak = F.err_metrics(whole, ref)
+    assert whole.shape == ref.shape and nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
