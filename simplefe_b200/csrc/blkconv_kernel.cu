@@ -15,6 +15,10 @@
 //              (blkconv.cxx:92-101), fused between the last forward and first inverse butterfly
 //   inverse  : the mirrored DIT passes with conjugated twiddles, then overlap discard + store.
 // No reordering pass is ever needed: forward leaves digit-reversed order, inverse consumes it.
+#include <cmath>
+#include <cstdlib>
+#include <vector>
+
 #include "sfe_fft.cuh"
 #include "kernels.h"
 
@@ -38,47 +42,64 @@ template <int N> struct Plan {
         for (int i = 0; i < p; i++) m /= radix(i);
         return m;
     }
+    // Twiddles are stored per pass as rows q = 1..R-1 of S = M/R entries, tw[q-1][j] = exp(-2 pi i j q / M): the
+    // threads of a warp hold consecutive j, so every twiddle load is one contiguous 128/256-byte piece of L1
+    // (the flat exp(-2 pi i k / N) table indexed by (N/M) j q cost up to 16 L1 wavefronts per load).
+    static __host__ __device__ constexpr int tw_off(int p)
+    {
+        int o = 0;
+        for (int i = 0; i < p; i++) o += (radix(i) - 1) * (size(i) / radix(i));
+        return o;
+    }
 };
 
 __device__ __forceinline__ int phi(int a) { return a + (a >> 4); }  // bank-conflict padding
+
+// input flavours the kernel is compiled for (one instantiation each: no per-sample format dispatch)
+enum { KF_I16 = 0, KF_U8 = 1, KF_C64 = 2, KF_REAL = 3 };
 
 struct Ctx {
     const BlkconvParams &p;
     int stream;     // stream row of this FFT
     long blk0;      // first output sample of this block
     bool active;
+    bool in_interior;    // all N input samples of the block lie in the current rows: no history, no zero fill
+    bool out_interior;   // all N - ov outputs of the block are valid
+    const void *in_base; // sample blk0 - ov of this stream's current row (interior blocks)
+    void *out_base;      // output sample blk0 of this stream
 };
 
-// source of pass 0 (forward): global memory, with format conversion, history and zero fill
-__device__ __forceinline__ float2 load_input(const Ctx &c, int i)
+template <int KF> __device__ __forceinline__ float2 load_at(const void *base, long i)
 {
-    if (!c.active) return make_float2(0.f, 0.f);
-    const long n = c.blk0 - c.p.ov + i;
-    if (c.p.in_real) {
-        if (n >= c.p.in.n) return make_float2(0.f, 0.f);
-        const float *cur = reinterpret_cast<const float *>(c.p.in.cur);
-        const float *hist = reinterpret_cast<const float *>(c.p.in.hist);
-        if (n >= 0) return make_float2(__ldg(cur + (long)c.stream * c.p.in.pitch + n), 0.f);
-        const long h = c.p.in.H + n;
-        return h < 0 ? make_float2(0.f, 0.f) : make_float2(__ldg(hist + (long)c.stream * c.p.in.H + h), 0.f);
-    }
-    return load_sample(c.p.in, c.stream, n);
+    if (KF == KF_I16) return cvt_i16(__ldg(reinterpret_cast<const uint32_t *>(base) + i));
+    if (KF == KF_U8) return cvt_u8(__ldg(reinterpret_cast<const uint16_t *>(base) + i));
+    if (KF == KF_C64) return __ldg(reinterpret_cast<const float2 *>(base) + i);
+    return make_float2(__ldg(reinterpret_cast<const float *>(base) + i), 0.f);
 }
 
-__device__ __forceinline__ void store_output(const Ctx &c, int i, float2 v)
+// source of pass 0 (forward): global memory, with format conversion, history and zero fill
+template <int KF> __device__ __forceinline__ float2 load_input(const Ctx &c, int i)
 {
-    if (!c.active || i < c.p.ov) return;                   // overlap discard
-    const long n = c.blk0 + (i - c.p.ov);
-    if (n >= c.p.in.n) return;
-    if (c.p.in_real)
-        reinterpret_cast<float *>(c.p.out)[(long)c.stream * c.p.out_pitch + n] = v.x;
-    else
-        reinterpret_cast<float2 *>(c.p.out)[(long)c.stream * c.p.out_pitch + n] = v;
+    if (c.in_interior) return load_at<KF>(c.in_base, i);
+    if (!c.active) return make_float2(0.f, 0.f);
+    const long n = c.blk0 - c.p.ov + i;
+    if (n >= c.p.in.n) return make_float2(0.f, 0.f);
+    if (n >= 0) return load_at<KF>(c.p.in.cur, (long)c.stream * c.p.in.pitch + n);
+    const long h = (long)c.p.in.H + n;
+    return h < 0 ? make_float2(0.f, 0.f) : load_at<KF>(c.p.in.hist, (long)c.stream * c.p.in.H + h);
+}
+
+template <int KF> __device__ __forceinline__ void store_output(const Ctx &c, int i, float2 v)
+{
+    if (i < c.p.ov) return;                                 // overlap discard
+    if (!c.out_interior && (!c.active || c.blk0 + (i - c.p.ov) >= c.p.in.n)) return;
+    if (KF == KF_REAL) reinterpret_cast<float *>(c.out_base)[i - c.p.ov] = v.x;
+    else reinterpret_cast<float2 *>(c.out_base)[i - c.p.ov] = v;
 }
 
 // ---- one forward (DIF) pass -------------------------------------------------------------------
 // P = pass index. FIRST: read from global. The last pass leaves its result in registers (vout).
-template <int N, int P, bool KEEP>
+template <int N, int P, bool KEEP, int KF>
 __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 (&keep)[16])
 {
     using PL = Plan<N>;
@@ -89,7 +110,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
         const int b = (beta / S) * M, j = beta % S;
         float2 v[R];
 #pragma unroll
-        for (int k = 0; k < R; k++) v[k] = P == 0 ? load_input(c, b + j + k * S) : X[phi(b + j + k * S)];
+        for (int k = 0; k < R; k++) v[k] = P == 0 ? load_input<KF>(c, b + j + k * S) : X[phi(b + j + k * S)];
         dft_dif<R, -1>(v);
 #pragma unroll
         for (int sl = 0; sl < R; sl++) {
@@ -97,7 +118,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
             (void)dummy;
             const int q = brev<R>(sl);
             float2 y = v[sl];
-            if (S > 1 && q != 0) y = cmul(y, __ldg(c.p.tw + (N / M) * j * q));
+            if (S > 1 && q != 0) y = cmul(y, __ldg(c.p.tw + PL::tw_off(P) + (q - 1) * S + j));
             if (KEEP) keep[u * R + q] = y;
             else X[phi(b + j + q * S)] = y;
         }
@@ -105,7 +126,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
 }
 
 // ---- one inverse (DIT) pass: exact mirror of fwd_pass<P> ----------------------------------------
-template <int N, int P, bool FROMREG>
+template <int N, int P, bool FROMREG, int KF>
 __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 (&keep)[16])
 {
     using PL = Plan<N>;
@@ -118,62 +139,69 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
 #pragma unroll
         for (int q = 0; q < R; q++) {
             float2 y = FROMREG ? keep[u * R + q] : X[phi(b + j + q * S)];
-            if (S > 1 && q != 0) y = cmul_conj(y, __ldg(c.p.tw + (N / M) * j * q));
+            if (S > 1 && q != 0) y = cmul_conj(y, __ldg(c.p.tw + PL::tw_off(P) + (q - 1) * S + j));
             v[q] = y;
         }
         dft_dif<R, +1>(v);
 #pragma unroll
         for (int sl = 0; sl < R; sl++) {
             const int k = brev<R>(sl);
-            if (P == 0) store_output(c, b + j + k * S, v[sl]);
+            if (P == 0) store_output<KF>(c, b + j + k * S, v[sl]);
             else X[phi(b + j + k * S)] = v[sl];
         }
     }
 }
 
-template <int N, int P> struct FwdChain {
+template <int N, int P, int KF> struct FwdChain {
     static __device__ __forceinline__ void run(float2 *X, int t, const Ctx &c, float2 (&keep)[16])
     {
         constexpr bool last = (P == Plan<N>::NP - 1);
-        fwd_pass<N, P, last>(X, t, c, keep);
+        fwd_pass<N, P, last, KF>(X, t, c, keep);
         if constexpr (!last) {
             __syncthreads();
-            FwdChain<N, P + 1>::run(X, t, c, keep);
+            FwdChain<N, P + 1, KF>::run(X, t, c, keep);
         }
     }
 };
 
-template <int N, int P> struct InvChain {
+template <int N, int P, int KF> struct InvChain {
     static __device__ __forceinline__ void run(float2 *X, int t, const Ctx &c, float2 (&keep)[16])
     {
         constexpr bool first = (P == Plan<N>::NP - 1);
-        inv_pass<N, P, first>(X, t, c, keep);
+        inv_pass<N, P, first, KF>(X, t, c, keep);
         if constexpr (P > 0) {
             __syncthreads();
-            InvChain<N, P - 1>::run(X, t, c, keep);
+            InvChain<N, P - 1, KF>::run(X, t, c, keep);
         }
     }
 };
 
-template <int N, int FPB>
-__global__ void __launch_bounds__(Plan<N>::TPF *FPB) blkconv_fft_kernel(const BlkconvParams p)
+template <int N, int FPB, int MINB, int KF>
+__global__ void __launch_bounds__(Plan<N>::TPF *FPB, MINB) blkconv_fft_kernel(const BlkconvParams p)
 {
     using PL = Plan<N>;
     extern __shared__ float2 smem[];
     const int f = threadIdx.x / PL::TPF, t = threadIdx.x % PL::TPF;
     const long id = (long)blockIdx.x * FPB + f;
     const long total = (long)p.n_streams * p.n_blocks;
-    Ctx c{p, 0, 0, id < total};
+    Ctx c{p, 0, 0, id < total, false, false, nullptr, nullptr};
     if (c.active) {
         c.stream = (int)(id / p.n_blocks);
         c.blk0 = (id % p.n_blocks) * (long)p.hop;
+        const long first = c.blk0 - p.ov;
+        c.in_interior = first >= 0 && first + N <= p.in.n;
+        c.out_interior = c.blk0 + (N - p.ov) <= p.in.n;
+        constexpr int EB = KF == KF_I16 ? 4 : KF == KF_U8 ? 2 : KF == KF_C64 ? 8 : 4;
+        c.in_base = static_cast<const char *>(p.in.cur) + ((long)c.stream * p.in.pitch + first) * EB;
+        c.out_base = static_cast<char *>(p.out) + ((long)c.stream * p.out_pitch + c.blk0) * (KF == KF_REAL ? 4 : 8);
     }
     float2 *X = smem + f * PL::PADN;
     float2 keep[16];
 
-    FwdChain<N, 0>::run(X, t, c, keep);
+    FwdChain<N, 0, KF>::run(X, t, c, keep);
 
-    // thread-private spectrum slice: last pass has S = 1, element index = R*beta + q
+    // thread-private spectrum slice: last pass has S = 1, element index = R*beta + q.  The tap spectrum is stored
+    // slot-major, hp[(u*R + q) * TPF + t], so that the threads of a warp read consecutive words.
     constexpr int RL = PL::radix(PL::NP - 1), NB = 16 / RL;
     if (p.mode == BLKCONV_MODE_SPECTRUM) {
         // tap spectrum in the kernel's own digit-reversed order, pre-scaled (blkconv.cxx:50,60-69)
@@ -183,7 +211,7 @@ __global__ void __launch_bounds__(Plan<N>::TPF *FPB) blkconv_fft_kernel(const Bl
 #pragma unroll
                 for (int q = 0; q < RL; q++) {
                     const float2 v = keep[u * RL + q];
-                    reinterpret_cast<float2 *>(p.out)[(t + u * PL::TPF) * RL + q] = make_float2(v.x * p.scale, v.y * p.scale);
+                    reinterpret_cast<float2 *>(p.out)[(u * RL + q) * PL::TPF + t] = make_float2(v.x * p.scale, v.y * p.scale);
                 }
         }
         return;
@@ -192,9 +220,9 @@ __global__ void __launch_bounds__(Plan<N>::TPF *FPB) blkconv_fft_kernel(const Bl
     for (int u = 0; u < NB; u++)
 #pragma unroll
         for (int q = 0; q < RL; q++)
-            keep[u * RL + q] = cmul(keep[u * RL + q], __ldg(p.hp + (t + u * PL::TPF) * RL + q));
+            keep[u * RL + q] = cmul(keep[u * RL + q], __ldg(p.hp + (u * RL + q) * PL::TPF + t));
 
-    InvChain<N, PL::NP - 1>::run(X, t, c, keep);
+    InvChain<N, PL::NP - 1, KF>::run(X, t, c, keep);
 }
 
 template <int N> int launch_n(const BlkconvParams &p, cudaStream_t st)
@@ -204,7 +232,12 @@ template <int N> int launch_n(const BlkconvParams &p, cudaStream_t st)
     const long total = (long)p.n_streams * p.n_blocks;
     if (total <= 0) return SFE_OK;
     const size_t smem = sizeof(float2) * PL::PADN * FPB;
-    auto kern = blkconv_fft_kernel<N, FPB>;
+    // resident CTAs per SM the register allocation must allow: 768 threads (85 registers each, no spills)
+    constexpr int MINB = PL::TPF * FPB <= 256 ? 768 / (PL::TPF * FPB) : 1;
+    void (*kern)(const BlkconvParams) =
+        p.in_real ? blkconv_fft_kernel<N, FPB, MINB, KF_REAL>
+                  : p.in.fmt == SFE_IN_I16 ? blkconv_fft_kernel<N, FPB, MINB, KF_I16>
+                                           : p.in.fmt == SFE_IN_U8 ? blkconv_fft_kernel<N, FPB, MINB, KF_U8> : blkconv_fft_kernel<N, FPB, MINB, KF_C64>;
     if (smem > 48 * 1024 &&
         !SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)))
         return SFE_ERR_CUDA;
@@ -214,7 +247,39 @@ template <int N> int launch_n(const BlkconvParams &p, cudaStream_t st)
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }
 
+template <int N> void tw_table_n(std::vector<float2> &h)
+{
+    using PL = Plan<N>;
+    h.assign((size_t)PL::tw_off(PL::NP) + 1, make_float2(1.f, 0.f));
+    for (int p = 0; p < PL::NP; p++) {
+        const int R = PL::radix(p), M = PL::size(p), S = M / R;
+        if (S <= 1) continue;
+        for (int q = 1; q < R; q++)
+            for (int j = 0; j < S; j++) {
+                const double a = -2.0 * M_PI * (double)j * (double)q / (double)M;
+                h[(size_t)PL::tw_off(p) + (size_t)(q - 1) * S + j] = make_float2((float)cos(a), (float)sin(a));
+            }
+    }
+}
+
 }  // namespace
+
+// host image of the per-pass twiddle rows the kernel for fft_len expects (Plan<N>::tw_off)
+bool blkconv_twiddle_table(int fft_len, std::vector<float2> &h)
+{
+    switch (fft_len) {
+        case 32: tw_table_n<32>(h); return true;
+        case 64: tw_table_n<64>(h); return true;
+        case 128: tw_table_n<128>(h); return true;
+        case 256: tw_table_n<256>(h); return true;
+        case 512: tw_table_n<512>(h); return true;
+        case 1024: tw_table_n<1024>(h); return true;
+        case 2048: tw_table_n<2048>(h); return true;
+        case 4096: tw_table_n<4096>(h); return true;
+        case 8192: tw_table_n<8192>(h); return true;
+        default: return false;
+    }
+}
 
 int launch_blkconv(int fft_len, const BlkconvParams &p, cudaStream_t st)
 {

@@ -55,14 +55,14 @@ static const float2 *twiddles(int dev, int N)
     std::lock_guard<std::mutex> lk(g_tw_mutex);
     auto it = g_tw.find({dev, N});
     if (it != g_tw.end()) return it->second;
-    std::vector<float2> h((size_t)N);
-    for (int k = 0; k < N; k++) {
-        const double a = -2.0 * M_PI * (double)k / (double)N;
-        h[k] = make_float2((float)cos(a), (float)sin(a));
+    std::vector<float2> h;
+    if (!blkconv_twiddle_table(N, h)) {
+        set_error("blkconv: fft_len must be a power of two in [32, 8192]");
+        return nullptr;
     }
     float2 *d = nullptr;
-    if (!SFE_CUDA(cudaMalloc(&d, sizeof(float2) * N))) return nullptr;
-    if (!SFE_CUDA(cudaMemcpy(d, h.data(), sizeof(float2) * N, cudaMemcpyHostToDevice))) return nullptr;
+    if (!SFE_CUDA(cudaMalloc(&d, sizeof(float2) * h.size()))) return nullptr;
+    if (!SFE_CUDA(cudaMemcpy(d, h.data(), sizeof(float2) * h.size(), cudaMemcpyHostToDevice))) return nullptr;
     g_tw[{dev, N}] = d;
     return d;
 }
@@ -376,6 +376,7 @@ extern "C" int sfe_polyphase_process(sfe_polyphase *h, const float *in, int n_in
         p.uniform = 0;
         p.sched = h->d_sched;
         p.exact = h->exact;
+        p.rate = rate;
         int rc = launch_poly_generic(p, h->st);
         if (rc != SFE_OK) return rc;
         if (!SFE_CUDA(cudaMemcpyAsync(out, h->d_out, sizeof(float) * n_out, cudaMemcpyDeviceToHost, h->st))) return SFE_ERR_CUDA;

@@ -350,6 +350,7 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             p.step = op.sched.step;
             p.sched = op.d_sched;
             p.exact = (c->flags & SFE_FLAG_EXACT) ? 1 : 0;
+            p.rate = op.rate;
             rc = launch_poly_generic(p, st);
         }
         if (rc != SFE_OK) return rc;

@@ -16,12 +16,13 @@ struct BlkconvParams {
     long n_blocks;        // FFT blocks per stream = ceil(n / hop)
     int hop;              // fft_len + 1 - n_taps (blkconv.cxx:47)
     int ov;               // n_taps - 1          (blkconv.cxx:48)
-    const float2 *tw;     // exp(-2 pi i k / N), k < N
+    const float2 *tw;     // per-pass twiddle rows (blkconv_twiddle_table)
     const float2 *hp;     // tap spectrum, kernel (digit-reversed) order, pre-scaled by 1/N
     int mode;
     float scale;          // spectrum mode: 1/N (blkconv.cxx:50)
 };
 int launch_blkconv(int fft_len, const BlkconvParams &p, cudaStream_t st);
+bool blkconv_twiddle_table(int fft_len, std::vector<float2> &host);
 
 // ---- K2g: generic polyphase stage, one thread per output (polyphase_kernel.cu) ------------------
 struct PolyParams {
@@ -38,6 +39,9 @@ struct PolyParams {
     long pos0, step;
     const SchedEntry *sched;  // device, n_out entries when !uniform
     int exact;            // reference operation order (separate multiply/add)
+    float rate;           // the stage's rate (input samples per output): sizes the tile when the schedule is a table
+    // filled by launch_poly_generic
+    int kt, jp, tap_bytes, span_cap;
 };
 int launch_poly_generic(const PolyParams &p, cudaStream_t st);
 

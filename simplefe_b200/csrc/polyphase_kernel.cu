@@ -7,16 +7,32 @@
 // with (pos_k, mu_k) from the data-independent float32 time walk (schedule.cpp).  Both reference
 // classes produce these numbers (bit-identically); `resample` merely evaluates all
 // L phases for every input first.  The kernels below compute retained outputs only.
+#include <algorithm>
+
 #include "kernels.h"
 
 namespace sfe {
 
 namespace {
 
+constexpr int POLY_NT = 128;                 // threads per CTA
+constexpr int POLY_SPAN_BYTES = 32 * 1024;   // staged input span per CTA
+constexpr int SPARSE_U = 8;                  // loads in flight per lane of the warp-per-output kernel
+
 // ---------------------------------------------------------------------------------------------
-// K2g: any L, any rate, table or closed-form schedule, complex or real rows.  One thread per
-// output; window read straight from global memory (L1/L2 serve the overlap between neighbours).
+// K2g: any L, any rate, table or closed-form schedule, complex or real rows.  poly_point is the direct
+// form (window read straight from global memory), used for tiles too sparse to stage.
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float2 load_real(const StreamView &v, int s, long n)   // float rows (single-object API)
+{
+    float xr = 0.f;
+    if (n < v.n) {
+        if (n >= 0) xr = __ldg(reinterpret_cast<const float *>(v.cur) + (long)s * v.pitch + n);
+        else if (v.H + n >= 0) xr = __ldg(reinterpret_cast<const float *>(v.hist) + (long)s * v.H + v.H + n);
+    }
+    return make_float2(xr, 0.f);
+}
+
 template <bool EXACT, bool REAL>
 __device__ __forceinline__ float2 poly_point(const PolyParams &p, int s, long pos)
 {
@@ -51,12 +67,27 @@ __device__ __forceinline__ float2 poly_point(const PolyParams &p, int s, long po
 }
 
 template <bool EXACT, bool REAL>
-__global__ void __launch_bounds__(128) poly_generic_kernel(const PolyParams p)
+__device__ __forceinline__ void poly_store(const PolyParams &p, int s, long k, float2 s0, float2 s1, float mu, bool have1)
 {
-    const long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= p.n_out) return;
-    long pos;
-    float mu;
+    float2 y;
+    if (EXACT) {
+        // get_sample(phase0,n0) * (1.0f-m_mu) + m_mu*get_sample(phase1,n1)   decimate.cxx:123
+        const float w0 = __fsub_rn(1.0f, mu);
+        y.x = __fadd_rn(__fmul_rn(s0.x, w0), __fmul_rn(mu, s1.x));
+        y.y = __fadd_rn(__fmul_rn(s0.y, w0), __fmul_rn(mu, s1.y));
+    } else if (have1) {
+        const float w0 = 1.0f - mu;
+        y.x = fmaf(mu, s1.x, s0.x * w0);
+        y.y = fmaf(mu, s1.y, s0.y * w0);
+    } else {
+        y = s0;  // mu == 0: s0*1 + 0*s1
+    }
+    if (REAL) reinterpret_cast<float *>(p.out)[(long)s * p.out_pitch + k] = y.x;
+    else reinterpret_cast<float2 *>(p.out)[(long)s * p.out_pitch + k] = y;
+}
+
+__device__ __forceinline__ void poly_sched(const PolyParams &p, long k, long &pos, float &mu)
+{
     if (p.uniform) {
         pos = p.pos0 + k * p.step;
         mu = 0.f;
@@ -65,25 +96,185 @@ __global__ void __launch_bounds__(128) poly_generic_kernel(const PolyParams p)
         pos = e.pos;
         mu = e.mu;
     }
+}
+
+__device__ __forceinline__ long floordiv(long a, int b)
+{
+    long q = a / b;
+    if (a - q * b < 0) q -= 1;
+    return q;
+}
+
+// Sparse outputs (the step is so large that the windows of neighbouring outputs hardly overlap and a tile's span does
+// not fit shared memory): one WARP per output.  Lanes split the taps, so the window is read as contiguous 128/256-byte
+// pieces instead of 32 scattered sectors per load, and a butterfly of shuffles adds the partial sums.  The summation
+// order differs from the reference's, so the EXACT flavour keeps one thread per output (poly_point).
+template <bool REAL>
+__global__ void __launch_bounds__(POLY_NT) poly_sparse_kernel(const PolyParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const long wid = ((long)blockIdx.x * POLY_NT + threadIdx.x) >> 5, nw = ((long)gridDim.x * POLY_NT) >> 5;
     for (int s = blockIdx.y; s < p.n_streams; s += gridDim.y) {
-        const float2 s0 = poly_point<EXACT, REAL>(p, s, pos);
-        float2 y;
-        if (EXACT) {
-            // get_sample(phase0,n0) * (1.0f-m_mu) + m_mu*get_sample(phase1,n1)   decimate.cxx:123
-            const float2 s1 = poly_point<EXACT, REAL>(p, s, pos + 1);
-            const float w0 = __fsub_rn(1.0f, mu);
-            y.x = __fadd_rn(__fmul_rn(s0.x, w0), __fmul_rn(mu, s1.x));
-            y.y = __fadd_rn(__fmul_rn(s0.y, w0), __fmul_rn(mu, s1.y));
-        } else if (mu != 0.f) {
-            const float2 s1 = poly_point<EXACT, REAL>(p, s, pos + 1);
-            const float w0 = 1.0f - mu;
-            y.x = fmaf(mu, s1.x, s0.x * w0);
-            y.y = fmaf(mu, s1.y, s0.y * w0);
-        } else {
-            y = s0;  // mu == 0: s0*1 + 0*s1
+        for (long k = wid; k < p.n_out; k += nw) {
+            long pos;
+            float mu;
+            poly_sched(p, k, pos, mu);
+            const long n0 = floordiv(pos, p.up);
+            const int ph0 = (int)(pos - n0 * p.up);
+            int ph1 = ph0 + 1, d = 0;
+            if (ph1 == p.up) { ph1 = 0; d = 1; }
+            const bool have1 = mu != 0.f;
+            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+            // SPARSE_U loads per lane are issued before the first FMA: a warp keeps its whole window in flight
+#pragma unroll 1
+            for (int pt = 0; pt < (have1 ? 2 : 1); pt++) {
+                const int ph = pt ? ph1 : ph0;
+                const long nn = pt ? n0 + d : n0;
+                const int nj = (p.n_taps - ph + p.up - 1) / p.up;          // taps of this phase
+                float2 acc = make_float2(0.f, 0.f);
+                for (int jb = 0; jb < nj; jb += 32 * SPARSE_U) {
+                    float2 x[SPARSE_U];
+                    float t[SPARSE_U];
+#pragma unroll
+                    for (int u = 0; u < SPARSE_U; u++) {
+                        const int j = jb + u * 32 + lane;
+                        const bool ok = j < nj;
+                        t[u] = ok ? __ldg(p.taps + ph + j * p.up) : 0.f;
+                        x[u] = !ok ? make_float2(0.f, 0.f) : REAL ? load_real(p.in, s, nn - j) : load_sample(p.in, s, nn - j);
+                    }
+#pragma unroll
+                    for (int u = 0; u < SPARSE_U; u++) {
+                        acc.x = fmaf(t[u], x[u].x, acc.x);
+                        if (!REAL) acc.y = fmaf(t[u], x[u].y, acc.y);
+                    }
+                }
+                if (pt) a1 = acc;
+                else a0 = acc;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a0.x += __shfl_xor_sync(0xffffffffu, a0.x, o);
+                if (!REAL) a0.y += __shfl_xor_sync(0xffffffffu, a0.y, o);
+                if (have1) {
+                    a1.x += __shfl_xor_sync(0xffffffffu, a1.x, o);
+                    if (!REAL) a1.y += __shfl_xor_sync(0xffffffffu, a1.y, o);
+                }
+            }
+            if (lane == 0) poly_store<false, REAL>(p, s, k, a0, a1, mu, have1);
         }
-        if (REAL) reinterpret_cast<float *>(p.out)[(long)s * p.out_pitch + k] = y.x;
-        else reinterpret_cast<float2 *>(p.out)[(long)s * p.out_pitch + k] = y;
+    }
+}
+
+// One CTA = p.kt consecutive outputs of one stream.  The input span those outputs touch and the taps (phase
+// major, tp[ph][j] = taps[ph + j*up], odd pitch) are staged in shared memory once; each thread then walks its
+// outputs' windows there, sharing every sample between the two interpolation points s(pos) and s(pos+1):
+// per tap 1 LDS.64 + 2 LDS.32 + 4 FMA instead of 4 global loads with bounds checks.  A tile whose span does not
+// fit (very large rate: windows of neighbouring outputs do not overlap anyway) reads global memory directly.
+template <bool EXACT, bool REAL>
+__global__ void __launch_bounds__(POLY_NT) poly_generic_kernel(const PolyParams p)
+{
+    extern __shared__ __align__(16) unsigned char poly_sm[];
+    float *tp = reinterpret_cast<float *>(poly_sm);                       // [up][jp]
+    float2 *xs2 = reinterpret_cast<float2 *>(poly_sm + p.tap_bytes);      // staged samples (complex rows)
+    float *xs1 = reinterpret_cast<float *>(poly_sm + p.tap_bytes);        // staged samples (real rows)
+
+    const long k0 = (long)blockIdx.x * p.kt;
+    const long k1 = min(k0 + (long)p.kt, p.n_out) - 1;
+    long pos_lo, pos_hi;
+    float mu_unused;
+    poly_sched(p, k0, pos_lo, mu_unused);
+    poly_sched(p, k1, pos_hi, mu_unused);
+    const int J = p.jp;                                                    // taps per phase (padded to odd)
+    const long n_lo = floordiv(pos_lo, p.up) - (J - 1);
+    const long n_hi = floordiv(pos_hi + 1, p.up);
+    const long span = n_hi - n_lo + 1;
+    const bool tiled = p.tap_bytes > 0 && span <= p.span_cap;
+
+    if (tiled)
+        for (int i = threadIdx.x; i < p.up * J; i += POLY_NT) {
+            const int ph = i / J, j = i - ph * J, m = ph + j * p.up;
+            tp[i] = m < p.n_taps ? __ldg(p.taps + m) : 0.f;
+        }
+
+    for (int s = blockIdx.y; s < p.n_streams; s += gridDim.y) {
+        if (!tiled) {
+            for (long k = k0 + threadIdx.x; k <= k1; k += POLY_NT) {
+                long pos;
+                float mu;
+                poly_sched(p, k, pos, mu);
+                const float2 s0 = poly_point<EXACT, REAL>(p, s, pos);
+                const bool have1 = EXACT || mu != 0.f;
+                const float2 s1 = have1 ? poly_point<EXACT, REAL>(p, s, pos + 1) : make_float2(0.f, 0.f);
+                poly_store<EXACT, REAL>(p, s, k, s0, s1, mu, have1);
+            }
+            continue;
+        }
+        __syncthreads();                                                   // previous stream's readers are done
+        if (REAL) {
+            for (int i = threadIdx.x; i < (int)span; i += POLY_NT) {
+                const long n = n_lo + i;
+                float xr = 0.f;
+                if (n < p.in.n) {
+                    if (n >= 0) xr = __ldg(reinterpret_cast<const float *>(p.in.cur) + (long)s * p.in.pitch + n);
+                    else if (p.in.H + n >= 0) xr = __ldg(reinterpret_cast<const float *>(p.in.hist) + (long)s * p.in.H + p.in.H + n);
+                }
+                xs1[i] = xr;
+            }
+        } else {
+            for (int i = threadIdx.x; i < (int)span; i += POLY_NT) xs2[i] = load_sample(p.in, s, n_lo + i);
+        }
+        __syncthreads();
+        for (long k = k0 + threadIdx.x; k <= k1; k += POLY_NT) {
+            long pos;
+            float mu;
+            poly_sched(p, k, pos, mu);
+            const long n0 = floordiv(pos, p.up);
+            const int ph0 = (int)(pos - n0 * p.up);
+            int ph1 = ph0 + 1, d = 0;                                      // s(pos+1): next phase, or phase 0 one sample on
+            if (ph1 == p.up) { ph1 = 0; d = 1; }
+            const int i0 = (int)(n0 - n_lo);
+            const float *t0 = tp + ph0 * J, *t1 = tp + ph1 * J;
+            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+            const bool have1 = EXACT || mu != 0.f;
+            if (EXACT) {
+                // reference order: ascending j, separate multiply and add, only the taps m < n_taps (decimate.cxx:132-140)
+                const int c0 = (p.n_taps - ph0 + p.up - 1) / p.up, c1 = (p.n_taps - ph1 + p.up - 1) / p.up;
+                for (int j = 0; j < c0; j++) {
+                    const float2 x = REAL ? make_float2(xs1[i0 - j], 0.f) : xs2[i0 - j];
+                    a0.x = __fadd_rn(a0.x, __fmul_rn(t0[j], x.x));
+                    if (!REAL) a0.y = __fadd_rn(a0.y, __fmul_rn(t0[j], x.y));
+                }
+                for (int j = 0; j < c1; j++) {
+                    const float2 x = REAL ? make_float2(xs1[i0 + d - j], 0.f) : xs2[i0 + d - j];
+                    a1.x = __fadd_rn(a1.x, __fmul_rn(t1[j], x.x));
+                    if (!REAL) a1.y = __fadd_rn(a1.y, __fmul_rn(t1[j], x.y));
+                }
+            } else if (!have1) {
+#pragma unroll 4
+                for (int j = 0; j < J; j++) {
+                    const float2 x = REAL ? make_float2(xs1[i0 - j], 0.f) : xs2[i0 - j];
+                    const float t = t0[j];
+                    a0.x = fmaf(t, x.x, a0.x);
+                    if (!REAL) a0.y = fmaf(t, x.y, a0.y);
+                }
+            } else {
+                float2 xp = REAL ? make_float2(xs1[i0 + d], 0.f) : xs2[i0 + d];   // staged: n0 + d <= n_hi
+#pragma unroll 4
+                for (int j = 0; j < J; j++) {
+                    const float2 x = REAL ? make_float2(xs1[i0 - j], 0.f) : xs2[i0 - j];
+                    const float2 xb = d ? xp : x;                          // s(pos+1) reads one sample later when it wraps
+                    const float ta = t0[j], tb = t1[j];
+                    a0.x = fmaf(ta, x.x, a0.x);
+                    a1.x = fmaf(tb, xb.x, a1.x);
+                    if (!REAL) {
+                        a0.y = fmaf(ta, x.y, a0.y);
+                        a1.y = fmaf(tb, xb.y, a1.y);
+                    }
+                    xp = x;
+                }
+            }
+            poly_store<EXACT, REAL>(p, s, k, a0, a1, mu, have1);
+        }
     }
 }
 
@@ -156,17 +347,46 @@ __global__ void __launch_bounds__(DNT) decim_fir_kernel(const DecimParams p)
 
 }  // namespace
 
-int launch_poly_generic(const PolyParams &p, cudaStream_t st)
+int launch_poly_generic(const PolyParams &p_in, cudaStream_t st)
 {
+    PolyParams p = p_in;
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
-    dim3 grid((unsigned)((p.n_out + 127) / 128), (unsigned)(p.n_streams < 32768 ? p.n_streams : 32768));
-    if (p.exact) {
-        if (p.in_real) poly_generic_kernel<true, true><<<grid, 128, 0, st>>>(p);
-        else poly_generic_kernel<true, false><<<grid, 128, 0, st>>>(p);
-    } else {
-        if (p.in_real) poly_generic_kernel<false, true><<<grid, 128, 0, st>>>(p);
-        else poly_generic_kernel<false, false><<<grid, 128, 0, st>>>(p);
+    // tile: as many outputs per CTA as keep the staged span under POLY_SPAN_BYTES (the span grows with the step)
+    const int eb = p.in_real ? 4 : 8;
+    const int J = (p.n_taps + p.up - 1) / p.up;
+    p.jp = J | 1;
+    const size_t tap_bytes = ((size_t)p.up * p.jp * sizeof(float) + 15) & ~(size_t)15;
+    double step = p.uniform ? (double)p.step : 0.0;                        // grid positions per output
+    if (!p.uniform) step = (double)p.rate * p.up;
+    const double per_out = step / p.up;                                    // input samples per output
+    const long cap = POLY_SPAN_BYTES / eb;
+    long kt = (long)((double)(cap - p.jp - 8) / (per_out * 1.01 + 1e-9));
+    kt = kt / POLY_NT * POLY_NT;
+    if (kt > 8 * POLY_NT) kt = 8 * POLY_NT;
+    while (kt > POLY_NT && (p.n_out + kt - 1) / kt * p.n_streams < 2 * 148) kt -= POLY_NT;   // small jobs: more CTAs
+    p.tap_bytes = (int)tap_bytes;
+    p.span_cap = (int)std::min<long>(cap, (long)((double)kt * per_out * 1.01) + p.jp + 8);
+    if (kt < POLY_NT || tap_bytes > 48 * 1024) {                           // no useful tile: direct global reads
+        kt = POLY_NT;
+        p.tap_bytes = 0;
+        p.span_cap = 0;
     }
+    p.kt = (int)kt;
+    if (!p.tap_bytes && !p.exact) {                                        // sparse outputs: one warp per output
+        const long warps = std::min<long>(p.n_out, 8L * 148 * 16 / std::max(1, std::min(p.n_streams, 64)) + 1);
+        dim3 grid((unsigned)((warps * 32 + POLY_NT - 1) / POLY_NT), (unsigned)(p.n_streams < 32768 ? p.n_streams : 32768));
+        if (p.in_real) poly_sparse_kernel<true><<<grid, POLY_NT, 0, st>>>(p);
+        else poly_sparse_kernel<false><<<grid, POLY_NT, 0, st>>>(p);
+        count_launch();
+        return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+    }
+    const size_t smem = p.tap_bytes ? tap_bytes + (size_t)p.span_cap * eb : 0;
+    dim3 grid((unsigned)((p.n_out + kt - 1) / kt), (unsigned)(p.n_streams < 32768 ? p.n_streams : 32768));
+    auto kern = p.exact ? (p.in_real ? poly_generic_kernel<true, true> : poly_generic_kernel<true, false>)
+                        : (p.in_real ? poly_generic_kernel<false, true> : poly_generic_kernel<false, false>);
+    if (smem > 48 * 1024 && !SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)))
+        return SFE_ERR_CUDA;
+    kern<<<grid, POLY_NT, smem, st>>>(p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }

@@ -385,3 +385,47 @@ def test_chain_u8_bank_chunk_invariance(gpu_lib, oracle_lib, S, N, splits):
     ref, _ = O.chain_run(iq, F.IN_U8, cfg["blkconv"], cfg["stage_a"], cfg["stage_b"], lib=oracle_lib)
     nrms, peak = F.err_metrics(whole, ref)
     assert whole.shape == ref.shape and nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
+
+
+# ---- generic polyphase kernel: tiled (dense outputs) and warp-per-output (sparse outputs) flavours ------------
+
+@pytest.mark.parametrize("cls,up,rate,blk,tapname", [("decimate", 3, 208.4, 4096, "rs512_l3"), ("resample", 3, 57.31, 1000, "rs512_l3"),
+                                                     ("decimate", 1, 2.5003, 4096, "taps31"), ("resample", 4, 1.77, 333, "taps31"),
+                                                     ("resample", 24, 26.7, 4096, "rs512_l24"), ("decimate", 1, 1.0, 512, "dec128")])
+def test_polyphase_objects_fast_order_vs_oracle(gpu_lib, oracle_lib, cls, up, rate, blk, tapname):
+    """default (non-exact) summation order of the single-object path: counts bit-exact, values within tolerance"""
+    from oracle import oracle as O
+    from simplefe_b200 import pydsp
+    rng = np.random.default_rng(11)
+    x = rng.normal(0, 0.3, 30011).astype(np.float32)
+    t = F.taps(tapname)
+    ref = getattr(O, cls.capitalize())(t, up, blk, lib=oracle_lib).stream(x, rate)
+    g = getattr(pydsp, cls)(t, up, blk)
+    out_len = int(np.floor(np.float32(blk) / np.float32(rate))) + 2
+    ys = []
+    for off in range(0, len(x), blk):
+        n, y = g.process(x[off:off + blk], out_len, rate)
+        ys.append(y[:n])
+    got = np.concatenate(ys)
+    assert len(got) == len(ref)
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
+
+
+@pytest.mark.parametrize("up,rate,tapname,S,N,fmt", [(3, 208.4, "rs512_l3", 5, 150001, F.IN_I16), (1, 2.5003, "taps31", 3, 40001, F.IN_F32),
+                                                      (4, 1.3, "taps31", 2, 9001, F.IN_U8), (24, 700.53, "rs512_l24", 3, 90001, F.IN_I16)])
+def test_chain_generic_stage_fractional_rates(gpu_lib, oracle_lib, up, rate, tapname, S, N, fmt):
+    """one decimate stage with a non-integral step over several streams: the tiled and the warp-per-output kernels,
+    fed in two calls (history and held-over outputs cross the seam)"""
+    from oracle import oracle as O
+    st = dict(klass=F.KLASS_DECIMATE, taps=F.taps(tapname), up=up, blk=4096, rate=rate)
+    cfg = dict(in_fmt=fmt, S=S, N=N, seed=77, stage_a=st)
+    iq = F.make_input(cfg)
+    ch = _chain(cfg)
+    assert "polyphase_generic" in ch.plan
+    cut = (N // 3) // 4096 * 4096 + 4096
+    got = np.concatenate([ch.process(iq[:, :cut]), ch.process(iq[:, cut:])], axis=1)
+    ref, _ = O.chain_run(iq, fmt, None, st, None, lib=oracle_lib)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
