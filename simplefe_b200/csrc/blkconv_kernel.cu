@@ -69,18 +69,25 @@ struct Ctx {
     void *out_base;      // output sample blk0 of this stream
 };
 
-template <int KF> __device__ __forceinline__ float2 load_at(const void *base, long i)
+template <int KF> struct RawOf { typedef uint32_t type; };
+template <> struct RawOf<KF_U8> { typedef uint16_t type; };
+template <> struct RawOf<KF_C64> { typedef float2 type; };
+template <> struct RawOf<KF_REAL> { typedef float type; };
+
+__device__ __forceinline__ float2 cvt_raw(uint32_t w) { return cvt_i16(w); }
+__device__ __forceinline__ float2 cvt_raw(uint16_t w) { return cvt_u8(w); }
+__device__ __forceinline__ float2 cvt_raw(float2 w) { return w; }
+__device__ __forceinline__ float2 cvt_raw(float w) { return make_float2(w, 0.f); }
+
+template <int KF> __device__ __forceinline__ typename RawOf<KF>::type load_raw_at(const void *base, long i)
 {
-    if (KF == KF_I16) return cvt_i16(__ldg(reinterpret_cast<const uint32_t *>(base) + i));
-    if (KF == KF_U8) return cvt_u8(__ldg(reinterpret_cast<const uint16_t *>(base) + i));
-    if (KF == KF_C64) return __ldg(reinterpret_cast<const float2 *>(base) + i);
-    return make_float2(__ldg(reinterpret_cast<const float *>(base) + i), 0.f);
+    return __ldg(reinterpret_cast<const typename RawOf<KF>::type *>(base) + i);
 }
+template <int KF> __device__ __forceinline__ float2 load_at(const void *base, long i) { return cvt_raw(load_raw_at<KF>(base, i)); }
 
 // source of pass 0 (forward): global memory, with format conversion, history and zero fill
 template <int KF> __device__ __forceinline__ float2 load_input(const Ctx &c, int i)
 {
-    if (c.in_interior) return load_at<KF>(c.in_base, i);
     if (!c.active) return make_float2(0.f, 0.f);
     const long n = c.blk0 - c.p.ov + i;
     if (n >= c.p.in.n) return make_float2(0.f, 0.f);
@@ -109,8 +116,21 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
         const int beta = t + u * PL::TPF;
         const int b = (beta / S) * M, j = beta % S;
         float2 v[R];
+        if (P == 0) {
+            if (c.in_interior) {   // all loads first, conversions after: R independent requests in flight per thread
+                typename RawOf<KF>::type raw[R];
 #pragma unroll
-        for (int k = 0; k < R; k++) v[k] = P == 0 ? load_input<KF>(c, b + j + k * S) : X[phi(b + j + k * S)];
+                for (int k = 0; k < R; k++) raw[k] = load_raw_at<KF>(c.in_base, b + j + k * S);
+#pragma unroll
+                for (int k = 0; k < R; k++) v[k] = cvt_raw(raw[k]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < R; k++) v[k] = load_input<KF>(c, b + j + k * S);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < R; k++) v[k] = X[phi(b + j + k * S)];
+        }
         dft_dif<R, -1>(v);
 #pragma unroll
         for (int sl = 0; sl < R; sl++) {

@@ -17,7 +17,6 @@ namespace {
 
 constexpr int POLY_NT = 128;                 // threads per CTA
 constexpr int POLY_SPAN_BYTES = 32 * 1024;   // staged input span per CTA
-constexpr int SPARSE_U = 8;                  // loads in flight per lane of the warp-per-output kernel
 
 // ---------------------------------------------------------------------------------------------
 // K2g: any L, any rate, table or closed-form schedule, complex or real rows.  poly_point is the direct
@@ -105,63 +104,22 @@ __device__ __forceinline__ long floordiv(long a, int b)
     return q;
 }
 
-// Sparse outputs (the step is so large that the windows of neighbouring outputs hardly overlap and a tile's span does
-// not fit shared memory): one WARP per output.  Lanes split the taps, so the window is read as contiguous 128/256-byte
-// pieces instead of 32 scattered sectors per load, and a butterfly of shuffles adds the partial sums.  The summation
-// order differs from the reference's, so the EXACT flavour keeps one thread per output (poly_point).
-template <bool REAL>
-__global__ void __launch_bounds__(POLY_NT) poly_sparse_kernel(const PolyParams p)
+// Sparse outputs (the step is so large that a tile's span does not fit shared memory and the windows of neighbouring
+// outputs hardly overlap): one thread per output straight from global memory.  (A warp-per-output flavour with
+// coalesced window reads and a shuffle reduction was measured at 2x the time: ~500 instructions per output.)
+template <bool EXACT, bool REAL>
+__global__ void __launch_bounds__(POLY_NT) poly_direct_kernel(const PolyParams p)
 {
-    const int lane = threadIdx.x & 31;
-    const long wid = ((long)blockIdx.x * POLY_NT + threadIdx.x) >> 5, nw = ((long)gridDim.x * POLY_NT) >> 5;
+    const long k = (long)blockIdx.x * POLY_NT + threadIdx.x;
+    if (k >= p.n_out) return;
+    long pos;
+    float mu;
+    poly_sched(p, k, pos, mu);
+    const bool have1 = EXACT || mu != 0.f;
     for (int s = blockIdx.y; s < p.n_streams; s += gridDim.y) {
-        for (long k = wid; k < p.n_out; k += nw) {
-            long pos;
-            float mu;
-            poly_sched(p, k, pos, mu);
-            const long n0 = floordiv(pos, p.up);
-            const int ph0 = (int)(pos - n0 * p.up);
-            int ph1 = ph0 + 1, d = 0;
-            if (ph1 == p.up) { ph1 = 0; d = 1; }
-            const bool have1 = mu != 0.f;
-            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
-            // SPARSE_U loads per lane are issued before the first FMA: a warp keeps its whole window in flight
-#pragma unroll 1
-            for (int pt = 0; pt < (have1 ? 2 : 1); pt++) {
-                const int ph = pt ? ph1 : ph0;
-                const long nn = pt ? n0 + d : n0;
-                const int nj = (p.n_taps - ph + p.up - 1) / p.up;          // taps of this phase
-                float2 acc = make_float2(0.f, 0.f);
-                for (int jb = 0; jb < nj; jb += 32 * SPARSE_U) {
-                    float2 x[SPARSE_U];
-                    float t[SPARSE_U];
-#pragma unroll
-                    for (int u = 0; u < SPARSE_U; u++) {
-                        const int j = jb + u * 32 + lane;
-                        const bool ok = j < nj;
-                        t[u] = ok ? __ldg(p.taps + ph + j * p.up) : 0.f;
-                        x[u] = !ok ? make_float2(0.f, 0.f) : REAL ? load_real(p.in, s, nn - j) : load_sample(p.in, s, nn - j);
-                    }
-#pragma unroll
-                    for (int u = 0; u < SPARSE_U; u++) {
-                        acc.x = fmaf(t[u], x[u].x, acc.x);
-                        if (!REAL) acc.y = fmaf(t[u], x[u].y, acc.y);
-                    }
-                }
-                if (pt) a1 = acc;
-                else a0 = acc;
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                a0.x += __shfl_xor_sync(0xffffffffu, a0.x, o);
-                if (!REAL) a0.y += __shfl_xor_sync(0xffffffffu, a0.y, o);
-                if (have1) {
-                    a1.x += __shfl_xor_sync(0xffffffffu, a1.x, o);
-                    if (!REAL) a1.y += __shfl_xor_sync(0xffffffffu, a1.y, o);
-                }
-            }
-            if (lane == 0) poly_store<false, REAL>(p, s, k, a0, a1, mu, have1);
-        }
+        const float2 s0 = poly_point<EXACT, REAL>(p, s, pos);
+        const float2 s1 = have1 ? poly_point<EXACT, REAL>(p, s, pos + 1) : make_float2(0.f, 0.f);
+        poly_store<EXACT, REAL>(p, s, k, s0, s1, mu, have1);
     }
 }
 
@@ -282,67 +240,154 @@ __global__ void __launch_bounds__(POLY_NT) poly_generic_kernel(const PolyParams 
 // K2d: y[k] = sum_j g[j] x[n_first + D k - j], complex rows, CUDA cores.
 // The CTA stages its input span in shared memory split into D polyphase planes
 // (plane r holds x[n_first + D m - r]), so that per plane the work is a plain FIR whose
-// neighbouring outputs share their window.  Each thread owns R consecutive outputs and slides a
-// register window over 8 taps at a time: 8*R*2 FMAs per (R+7) 64-bit shared loads.
+// neighbouring outputs share their window.  Each thread owns DR consecutive outputs and slides a
+// register window over 8 taps at a time.  A complex sample is one 64-bit word and a tap is stored as the pair
+// (g, g), so one packed FFMA2 advances the real and the imaginary sum: 64 FFMA2 per 15 LDS.64 + 4 LDS.128.
+// Integer samples are converted exactly (exponent trick) while staging; their scale lives in the taps.
 // ---------------------------------------------------------------------------------------------
 constexpr int DR = 8;     // outputs per thread
 constexpr int DNT = 128;  // threads per CTA
 constexpr int DKT = DR * DNT;
+constexpr int DSU = 8;    // staging: loads in flight per thread
 
-__device__ __forceinline__ int dphi(int a) { return a + a / DR; }
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 d_pack2(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ f32x2 d_ffma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 d_fadd2(f32x2 a, f32x2 b)
+{
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
 
+template <int FMT> struct DRaw { typedef uint32_t type; };
+template <> struct DRaw<SFE_IN_U8> { typedef uint16_t type; };
+template <> struct DRaw<SFE_IN_F32> { typedef f32x2 type; };
+
+// raw word -> (I, Q) as a packed pair of exact floats (unscaled integers for the integer formats)
+__device__ __forceinline__ f32x2 d_cvt(uint32_t w)     // int16 I,Q: bits 0x4B40_0000 | (s ^ 0x8000) = 12582912 + 32768 + s
+{
+    const uint32_t a = w ^ 0x80008000u, K = 0x4B400000u;
+    return d_fadd2(d_pack2(__uint_as_float(__byte_perm(a, K, 0x7610)), __uint_as_float(__byte_perm(a, K, 0x7632))),
+                   d_pack2(-12615680.0f, -12615680.0f));
+}
+__device__ __forceinline__ f32x2 d_cvt(uint16_t w)     // u8 I,Q: bits 0x4B00_0000 | b = 8388608 + b; value b - 128
+{
+    const uint32_t K = 0x4B000000u;
+    return d_fadd2(d_pack2(__uint_as_float(__byte_perm((uint32_t)w, K, 0x7650)), __uint_as_float(__byte_perm((uint32_t)w, K, 0x7651))),
+                   d_pack2(-8388736.0f, -8388736.0f));
+}
+__device__ __forceinline__ f32x2 d_cvt(f32x2 w) { return w; }
+
+template <int FMT> __device__ __forceinline__ f32x2 d_load_slow(const StreamView &v, int s, long i)
+{
+    typedef typename DRaw<FMT>::type RT;
+    if (i >= v.n) return 0ull;
+    if (i >= 0) return d_cvt(__ldg(reinterpret_cast<const RT *>(v.cur) + (long)s * v.pitch + i));
+    const long h = (long)v.H + i;
+    if (h < 0) return 0ull;
+    return d_cvt(__ldg(reinterpret_cast<const RT *>(v.hist) + (long)s * v.H + h));
+}
+
+template <int FMT>
 __global__ void __launch_bounds__(DNT) decim_fir_kernel(const DecimParams p)
 {
+    typedef typename DRaw<FMT>::type RT;
     extern __shared__ __align__(16) unsigned char smraw[];
     const int D = p.D, QLP = p.QLP;
     const int ML = DKT + QLP - 1;              // samples per plane
-    const int PITCH = dphi(ML) + 1;
-    float *gs = reinterpret_cast<float *>(smraw);                       // [D][QLP]
-    float2 *xs = reinterpret_cast<float2 *>(smraw + sizeof(float) * D * QLP);  // [D][PITCH]
+    const int PITCH = ML + ML / 8 + 1;         // one pad word per 8 entries: window loads of a warp are conflict free
+    f32x2 *gs = reinterpret_cast<f32x2 *>(smraw);                       // [D][QLP] pairs (g, g), scaled
+    f32x2 *xs = gs + D * QLP;                                           // [D][PITCH]
 
-    for (int i = threadIdx.x; i < D * QLP; i += DNT) gs[i] = __ldg(p.gp + i);
+    const float scale = FMT == SFE_IN_I16 ? 1.0f / 32767.0f : FMT == SFE_IN_U8 ? 1.0f / 127.0f : 1.0f;
+    for (int i = threadIdx.x; i < D * QLP; i += DNT) {
+        const float g = __ldg(p.gp + i) * scale;
+        gs[i] = d_pack2(g, g);
+    }
 
     const long k0 = (long)blockIdx.x * DKT;
-    const int s = blockIdx.y;
     // x index of (plane r, entry mm): n_first + D*(k0 - QLP + 1 + mm) - r ; enumerate e = mm*D + (D-1-r)
     const long xbase = p.n_first + (long)D * (k0 - QLP + 1) - (D - 1);
     const int total = D * ML;
-    for (int e = threadIdx.x; e < total; e += DNT) {
-        const int mm = e / D, r = D - 1 - (e - mm * D);
-        xs[r * PITCH + dphi(mm)] = load_sample(p.in, s, xbase + e);
-    }
-    __syncthreads();
+    const bool interior = xbase >= 0 && xbase + total <= p.in.n;        // no history, no zero fill
+    const int dm = DNT / D, dr = DNT % D;
 
-    float2 acc[DR];
+    for (int s = blockIdx.y; s < p.n_streams; s += gridDim.y) {
+        if (s != (int)blockIdx.y) __syncthreads();                      // the previous stream's readers are done
+        int mm = threadIdx.x / D, rr = threadIdx.x % D;                 // e = mm*D + rr, plane r = D-1-rr
+        if (interior) {
+            const RT *src = reinterpret_cast<const RT *>(p.in.cur) + (long)s * p.in.pitch + xbase;
+            for (int e0 = threadIdx.x; e0 < total; e0 += DNT * DSU) {
+                RT raw[DSU];
 #pragma unroll
-    for (int i = 0; i < DR; i++) acc[i] = make_float2(0.f, 0.f);
-
-    const int a0 = threadIdx.x * DR + QLP - 1 - 7;  // window start for chunk qc = 0
-    for (int r = 0; r < D; r++) {
-        const float2 *xr = xs + r * PITCH;
-        const float *gr = gs + r * QLP;
-        for (int qc = 0; qc < QLP; qc += 8) {
-            const float4 ga = *reinterpret_cast<const float4 *>(gr + qc);
-            const float4 gb = *reinterpret_cast<const float4 *>(gr + qc + 4);
-            const float g[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
-            float2 w[DR + 7];
-            const int a = a0 - qc;
-#pragma unroll
-            for (int c = 0; c < DR + 7; c++) w[c] = xr[dphi(a + c)];
-#pragma unroll
-            for (int d = 0; d < 8; d++)
-#pragma unroll
-                for (int i = 0; i < DR; i++) {
-                    acc[i].x = fmaf(g[d], w[7 - d + i].x, acc[i].x);
-                    acc[i].y = fmaf(g[d], w[7 - d + i].y, acc[i].y);
+                for (int u = 0; u < DSU; u++) {
+                    const int e = e0 + u * DNT;
+                    raw[u] = e < total ? __ldg(src + e) : RT();
                 }
+#pragma unroll
+                for (int u = 0; u < DSU; u++) {
+                    if (e0 + u * DNT < total) xs[(D - 1 - rr) * PITCH + mm + (mm >> 3)] = d_cvt(raw[u]);
+                    mm += dm;
+                    rr += dr;
+                    if (rr >= D) { rr -= D; mm++; }
+                }
+            }
+        } else {
+            for (int e = threadIdx.x; e < total; e += DNT) {
+                xs[(D - 1 - rr) * PITCH + mm + (mm >> 3)] = d_load_slow<FMT>(p.in, s, xbase + e);
+                mm += dm;
+                rr += dr;
+                if (rr >= D) { rr -= D; mm++; }
+            }
+        }
+        __syncthreads();
+
+        f32x2 acc[DR];
+#pragma unroll
+        for (int i = 0; i < DR; i++) acc[i] = 0ull;
+        // window start for chunk qc = 0 is entry a0 = tid*DR + QLP - 8, a multiple of 8: padded index a0/8*9
+        const int b0 = (threadIdx.x * DR + QLP - 8) / 8 * 9;
+        for (int r = 0; r < D; r++) {
+            const f32x2 *xr = xs + r * PITCH + b0;
+            const f32x2 *gr = gs + r * QLP;
+            for (int qc = 0; qc < QLP; qc += 8, xr -= 9) {
+                f32x2 g[8], w[DR + 7];
+#pragma unroll
+                for (int d = 0; d < 8; d += 2) {
+                    const ulonglong2 t = *reinterpret_cast<const ulonglong2 *>(gr + qc + d);
+                    g[d] = t.x;
+                    g[d + 1] = t.y;
+                }
+#pragma unroll
+                for (int c = 0; c < DR + 7; c++) w[c] = xr[c + (c >> 3)];
+#pragma unroll
+                for (int d = 0; d < 8; d++)
+#pragma unroll
+                    for (int i = 0; i < DR; i++) acc[i] = d_ffma2(g[d], w[7 - d + i], acc[i]);
+            }
+        }
+        const long kk = k0 + (long)threadIdx.x * DR;
+        f32x2 *o = reinterpret_cast<f32x2 *>(p.out + (long)s * p.out_pitch + kk);
+        if (kk + DR <= p.n_out && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+#pragma unroll
+            for (int i = 0; i < DR; i += 2) *reinterpret_cast<ulonglong2 *>(o + i) = make_ulonglong2(acc[i], acc[i + 1]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < DR; i++)
+                if (kk + i < p.n_out) o[i] = acc[i];
         }
     }
-    const long kk = k0 + (long)threadIdx.x * DR;
-    float2 *o = p.out + (long)s * p.out_pitch + kk;
-#pragma unroll
-    for (int i = 0; i < DR; i++)
-        if (kk + i < p.n_out) o[i] = acc[i];
 }
 
 }  // namespace
@@ -372,11 +417,11 @@ int launch_poly_generic(const PolyParams &p_in, cudaStream_t st)
         p.span_cap = 0;
     }
     p.kt = (int)kt;
-    if (!p.tap_bytes && !p.exact) {                                        // sparse outputs: one warp per output
-        const long warps = std::min<long>(p.n_out, 8L * 148 * 16 / std::max(1, std::min(p.n_streams, 64)) + 1);
-        dim3 grid((unsigned)((warps * 32 + POLY_NT - 1) / POLY_NT), (unsigned)(p.n_streams < 32768 ? p.n_streams : 32768));
-        if (p.in_real) poly_sparse_kernel<true><<<grid, POLY_NT, 0, st>>>(p);
-        else poly_sparse_kernel<false><<<grid, POLY_NT, 0, st>>>(p);
+    if (!p.tap_bytes) {                                                    // sparse outputs: one thread per output
+        dim3 grid((unsigned)((p.n_out + POLY_NT - 1) / POLY_NT), (unsigned)(p.n_streams < 32768 ? p.n_streams : 32768));
+        auto kd = p.exact ? (p.in_real ? poly_direct_kernel<true, true> : poly_direct_kernel<true, false>)
+                          : (p.in_real ? poly_direct_kernel<false, true> : poly_direct_kernel<false, false>);
+        kd<<<grid, POLY_NT, 0, st>>>(p);
         count_launch();
         return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
     }
@@ -395,17 +440,17 @@ int launch_decim_fir(const DecimParams &p, cudaStream_t st)
 {
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
     const int ML = DKT + p.QLP - 1;
-    const int PITCH = ML + ML / DR + 1;
-    const size_t smem = sizeof(float) * p.D * p.QLP + sizeof(float2) * (size_t)p.D * PITCH;
-    if (smem > 220 * 1024 || p.n_streams > 65535) {
+    const int PITCH = ML + ML / 8 + 1;
+    const size_t smem = sizeof(float2) * (size_t)p.D * p.QLP + sizeof(float2) * (size_t)p.D * PITCH;
+    if (smem > 220 * 1024 || DNT / p.D < 1) {
         set_error("decim_fir: tile does not fit shared memory (D * taps too large)");
         return SFE_ERR_ARG;
     }
-    if (smem > 48 * 1024 &&
-        !SFE_CUDA(cudaFuncSetAttribute(decim_fir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)))
+    auto kern = p.in.fmt == SFE_IN_I16 ? decim_fir_kernel<SFE_IN_I16> : p.in.fmt == SFE_IN_U8 ? decim_fir_kernel<SFE_IN_U8> : decim_fir_kernel<SFE_IN_F32>;
+    if (smem > 48 * 1024 && !SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)))
         return SFE_ERR_CUDA;
-    dim3 grid((unsigned)((p.n_out + DKT - 1) / DKT), (unsigned)p.n_streams);
-    decim_fir_kernel<<<grid, DNT, smem, st>>>(p);
+    dim3 grid((unsigned)((p.n_out + DKT - 1) / DKT), (unsigned)(p.n_streams < 32768 ? p.n_streams : 32768));
+    kern<<<grid, DNT, smem, st>>>(p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }
