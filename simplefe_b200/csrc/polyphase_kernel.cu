@@ -8,6 +8,7 @@
 // classes produce these numbers (bit-identically); `resample` merely evaluates all
 // L phases for every input first.  The kernels below compute retained outputs only.
 #include <algorithm>
+#include <cstdlib>
 
 #include "kernels.h"
 
@@ -248,7 +249,7 @@ __global__ void __launch_bounds__(POLY_NT) poly_generic_kernel(const PolyParams 
 constexpr int DR = 8;     // outputs per thread
 constexpr int DNT = 128;  // threads per CTA
 constexpr int DKT = DR * DNT;
-constexpr int DSU = 8;    // staging: loads in flight per thread
+constexpr int DSU = 16;   // staging: loads in flight per thread
 
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 d_pack2(float lo, float hi)
@@ -299,16 +300,67 @@ template <int FMT> __device__ __forceinline__ f32x2 d_load_slow(const StreamView
     return d_cvt(__ldg(reinterpret_cast<const RT *>(v.hist) + (long)s * v.H + h));
 }
 
-template <int FMT>
+// Tile layout in shared memory: the span in natural order, sample e of the tile at word e + (e >> 6) (one pad word
+// per 64 samples).  Staging is then a straight coalesced copy, and for D = 8 the windows of the 32 lanes (8 outputs =
+// 64 samples apart) start 65 words apart: every LDS.64 of the inner loop is conflict free.  Plane r, entry m of the
+// polyphase view is sample m*D + (D-1-r).
+__device__ __forceinline__ int dphys(int e) { return e + (e >> 6); }
+
+// The inner product of one thread: DR outputs, all planes and tap chunks; per chunk 15 window words and 8 tap pairs
+// feed 64 FFMA2.  (Explicit double buffering of the chunk loads was measured slower: 128 registers, 3.55 vs 3.28 ms.)
+template <int DT>
+__device__ __forceinline__ void decim_load_chunk(const f32x2 *xs, const f32x2 *gs, int D, int QLP, int a0, int ch, int cpp,
+                                                 f32x2 (&g)[8], f32x2 (&w)[DR + 7])
+{
+    const int r = ch / cpp, qc = (ch - r * cpp) * 8;
+    const f32x2 *gr = gs + r * QLP + qc;
+#pragma unroll
+    for (int d = 0; d < 8; d += 2) {
+        const ulonglong2 t = *reinterpret_cast<const ulonglong2 *>(gr + d);
+        g[d] = t.x;
+        g[d + 1] = t.y;
+    }
+    if (DT == 8) {   // (a + c)*8 + 7 - r: a*8 is a multiple of 64, so the pad term splits off at compile time
+        const f32x2 *xr = xs + dphys((a0 - qc) * 8) + (7 - r);
+#pragma unroll
+        for (int c = 0; c < DR + 7; c++) w[c] = xr[c * 8 + (c >> 3)];
+    } else {
+        const int e = (a0 - qc) * D + (D - 1 - r);
+#pragma unroll
+        for (int c = 0; c < DR + 7; c++) w[c] = xs[dphys(e + c * D)];
+    }
+}
+__device__ __forceinline__ void decim_fma_chunk(const f32x2 (&g)[8], const f32x2 (&w)[DR + 7], f32x2 (&acc)[DR])
+{
+#pragma unroll
+    for (int d = 0; d < 8; d++)
+#pragma unroll
+        for (int i = 0; i < DR; i++) acc[i] = d_ffma2(g[d], w[7 - d + i], acc[i]);
+}
+template <int DT>
+__device__ __forceinline__ void decim_compute(const f32x2 *xs, const f32x2 *gs, int D, int QLP, f32x2 (&acc)[DR])
+{
+#pragma unroll
+    for (int i = 0; i < DR; i++) acc[i] = 0ull;
+    // chunk qc of plane r reads entries a + c, c = 0..14, a = tid*DR + QLP - 8 - qc (a multiple of 8)
+    const int a0 = threadIdx.x * DR + QLP - 8;
+    const int cpp = QLP / 8, nch = D * cpp;
+    for (int ch = 0; ch < nch; ch++) {
+        f32x2 g[8], w[DR + 7];
+        decim_load_chunk<DT>(xs, gs, D, QLP, a0, ch, cpp, g, w);
+        decim_fma_chunk(g, w, acc);
+    }
+}
+
+template <int FMT, int DT>     // DT: decimation known at compile time (0 = any, from the parameters)
 __global__ void __launch_bounds__(DNT) decim_fir_kernel(const DecimParams p)
 {
     typedef typename DRaw<FMT>::type RT;
     extern __shared__ __align__(16) unsigned char smraw[];
-    const int D = p.D, QLP = p.QLP;
+    const int D = DT ? DT : p.D, QLP = p.QLP;
     const int ML = DKT + QLP - 1;              // samples per plane
-    const int PITCH = ML + ML / 8 + 1;         // one pad word per 8 entries: window loads of a warp are conflict free
     f32x2 *gs = reinterpret_cast<f32x2 *>(smraw);                       // [D][QLP] pairs (g, g), scaled
-    f32x2 *xs = gs + D * QLP;                                           // [D][PITCH]
+    f32x2 *xs = gs + D * QLP;                                           // dphys(D * ML) words
 
     const float scale = FMT == SFE_IN_I16 ? 1.0f / 32767.0f : FMT == SFE_IN_U8 ? 1.0f / 127.0f : 1.0f;
     for (int i = threadIdx.x; i < D * QLP; i += DNT) {
@@ -317,66 +369,30 @@ __global__ void __launch_bounds__(DNT) decim_fir_kernel(const DecimParams p)
     }
 
     const long k0 = (long)blockIdx.x * DKT;
-    // x index of (plane r, entry mm): n_first + D*(k0 - QLP + 1 + mm) - r ; enumerate e = mm*D + (D-1-r)
+    // tile sample e is x[xbase + e]; (plane r, entry mm) = sample mm*D + (D-1-r) = x[n_first + D*(k0 - QLP + 1 + mm) - r]
     const long xbase = p.n_first + (long)D * (k0 - QLP + 1) - (D - 1);
     const int total = D * ML;
     const bool interior = xbase >= 0 && xbase + total <= p.in.n;        // no history, no zero fill
-    const int dm = DNT / D, dr = DNT % D;
 
     for (int s = blockIdx.y; s < p.n_streams; s += gridDim.y) {
         if (s != (int)blockIdx.y) __syncthreads();                      // the previous stream's readers are done
-        int mm = threadIdx.x / D, rr = threadIdx.x % D;                 // e = mm*D + rr, plane r = D-1-rr
         if (interior) {
             const RT *src = reinterpret_cast<const RT *>(p.in.cur) + (long)s * p.in.pitch + xbase;
             for (int e0 = threadIdx.x; e0 < total; e0 += DNT * DSU) {
                 RT raw[DSU];
 #pragma unroll
-                for (int u = 0; u < DSU; u++) {
-                    const int e = e0 + u * DNT;
-                    raw[u] = e < total ? __ldg(src + e) : RT();
-                }
+                for (int u = 0; u < DSU; u++) raw[u] = e0 + u * DNT < total ? __ldg(src + e0 + u * DNT) : RT();
 #pragma unroll
-                for (int u = 0; u < DSU; u++) {
-                    if (e0 + u * DNT < total) xs[(D - 1 - rr) * PITCH + mm + (mm >> 3)] = d_cvt(raw[u]);
-                    mm += dm;
-                    rr += dr;
-                    if (rr >= D) { rr -= D; mm++; }
-                }
+                for (int u = 0; u < DSU; u++)
+                    if (e0 + u * DNT < total) xs[dphys(e0 + u * DNT)] = d_cvt(raw[u]);
             }
         } else {
-            for (int e = threadIdx.x; e < total; e += DNT) {
-                xs[(D - 1 - rr) * PITCH + mm + (mm >> 3)] = d_load_slow<FMT>(p.in, s, xbase + e);
-                mm += dm;
-                rr += dr;
-                if (rr >= D) { rr -= D; mm++; }
-            }
+            for (int e = threadIdx.x; e < total; e += DNT) xs[dphys(e)] = d_load_slow<FMT>(p.in, s, xbase + e);
         }
         __syncthreads();
 
         f32x2 acc[DR];
-#pragma unroll
-        for (int i = 0; i < DR; i++) acc[i] = 0ull;
-        // window start for chunk qc = 0 is entry a0 = tid*DR + QLP - 8, a multiple of 8: padded index a0/8*9
-        const int b0 = (threadIdx.x * DR + QLP - 8) / 8 * 9;
-        for (int r = 0; r < D; r++) {
-            const f32x2 *xr = xs + r * PITCH + b0;
-            const f32x2 *gr = gs + r * QLP;
-            for (int qc = 0; qc < QLP; qc += 8, xr -= 9) {
-                f32x2 g[8], w[DR + 7];
-#pragma unroll
-                for (int d = 0; d < 8; d += 2) {
-                    const ulonglong2 t = *reinterpret_cast<const ulonglong2 *>(gr + qc + d);
-                    g[d] = t.x;
-                    g[d + 1] = t.y;
-                }
-#pragma unroll
-                for (int c = 0; c < DR + 7; c++) w[c] = xr[c + (c >> 3)];
-#pragma unroll
-                for (int d = 0; d < 8; d++)
-#pragma unroll
-                    for (int i = 0; i < DR; i++) acc[i] = d_ffma2(g[d], w[7 - d + i], acc[i]);
-            }
-        }
+        decim_compute<DT>(xs, gs, D, QLP, acc);
         const long kk = k0 + (long)threadIdx.x * DR;
         f32x2 *o = reinterpret_cast<f32x2 *>(p.out + (long)s * p.out_pitch + kk);
         if (kk + DR <= p.n_out && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
@@ -388,6 +404,12 @@ __global__ void __launch_bounds__(DNT) decim_fir_kernel(const DecimParams p)
                 if (kk + i < p.n_out) o[i] = acc[i];
         }
     }
+}
+
+typedef void (*DecimKernel)(const DecimParams);
+template <int FMT> DecimKernel decim_pick(int D)
+{
+    return D == 8 ? decim_fir_kernel<FMT, 8> : decim_fir_kernel<FMT, 0>;
 }
 
 }  // namespace
@@ -440,13 +462,13 @@ int launch_decim_fir(const DecimParams &p, cudaStream_t st)
 {
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
     const int ML = DKT + p.QLP - 1;
-    const int PITCH = ML + ML / 8 + 1;
-    const size_t smem = sizeof(float2) * (size_t)p.D * p.QLP + sizeof(float2) * (size_t)p.D * PITCH;
-    if (smem > 220 * 1024 || DNT / p.D < 1) {
+    const int words = p.D * ML + (p.D * ML >> 6) + 2;
+    const size_t smem = sizeof(float2) * (size_t)p.D * p.QLP + sizeof(float2) * (size_t)words;
+    if (smem > 220 * 1024) {
         set_error("decim_fir: tile does not fit shared memory (D * taps too large)");
         return SFE_ERR_ARG;
     }
-    auto kern = p.in.fmt == SFE_IN_I16 ? decim_fir_kernel<SFE_IN_I16> : p.in.fmt == SFE_IN_U8 ? decim_fir_kernel<SFE_IN_U8> : decim_fir_kernel<SFE_IN_F32>;
+    DecimKernel kern = p.in.fmt == SFE_IN_I16 ? decim_pick<SFE_IN_I16>(p.D) : p.in.fmt == SFE_IN_U8 ? decim_pick<SFE_IN_U8>(p.D) : decim_pick<SFE_IN_F32>(p.D);
     if (smem > 48 * 1024 && !SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)))
         return SFE_ERR_CUDA;
     dim3 grid((unsigned)((p.n_out + DKT - 1) / DKT), (unsigned)(p.n_streams < 32768 ? p.n_streams : 32768));

@@ -13,6 +13,7 @@ int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t 
     const int64_t base = base_in * (int64_t)up;
     float t = (float)st.pos + st.mu;          // decimate.cxx:73  (float t = m_pos + m_mu)
     const float step = rate * (float)up;               // rate * m_up_ratio, rounded to float
+    const int64_t lim = (int64_t)n_in * up;
     if (st.held) {                                     // decimate.cxx:96-100
         // held-over output: left point is the last grid position of the previous call (-1),
         // right point is (phase 0, n 0); weight is the mu saved with it
@@ -25,10 +26,10 @@ int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t 
         const float tf = t;
         st.pos = (int)floorf(tf);                      // decimate.cxx:106
         st.mu = tf - (float)st.pos;                    // decimate.cxx:107
-        const int n0 = st.pos / up;                    // C truncating division, as the reference
-        const int n1 = (st.pos + 1) / up;
-        if (n0 >= n_in || n_out >= out_len) break;     // decimate.cxx:115
-        if (n1 >= n_in) {                              // decimate.cxx:118-121
+        // n0 = pos / up and n1 = (pos + 1) / up (C truncating division, decimate.cxx:109-113) are only compared
+        // with n_in: pos / up >= n_in  <=>  pos >= n_in * up for any sign of pos, so the walk needs no division
+        if (st.pos >= lim || n_out >= out_len) break;  // decimate.cxx:115
+        if (st.pos + 1 >= lim) {                       // decimate.cxx:118-121
             st.held = true;
             break;
         }
@@ -52,6 +53,20 @@ void walk_batch(WalkState &st, int up, int blk, float rate, int64_t n_in, Schedu
         s.memo_up = up;
         s.memo_out_len = out_len;
         s.memo_rate = rate;
+    }
+    const float stepf = rate * (float)up;
+    if (stepf != floorf(stepf)) {
+        // fractional step: (pos, mu, held) never repeats, so memoising calls only costs allocations; walk straight
+        // into the entry list.  Such a schedule is never closed-form (mu != 0 somewhere).
+        std::vector<SchedEntry> scratch;
+        std::vector<SchedEntry> &dst = want_entries ? s.e : scratch;
+        if (want_entries) dst.reserve((size_t)((double)n_in / (double)rate) + (size_t)(n_in / blk) * 2 + 8);
+        for (int64_t off = 0; off < n_in; off += blk) {
+            const int n = (int)((n_in - off) < blk ? (n_in - off) : blk);
+            if (!want_entries) scratch.clear();
+            s.count += walk_call(st, up, n, out_len, rate, off, dst);
+        }
+        return;
     }
     bool uni = true, have_prev = false;
     int64_t d = 0, prev = 0, first = 0;
