@@ -22,6 +22,8 @@
 //   up to four outputs are live per lane (their windows overlap); accumulators rotate as outputs finish.
 #include <cuda.h>
 
+#include <algorithm>
+#include <cstdlib>
 #include <map>
 #include <mutex>
 
@@ -559,7 +561,7 @@ int bank_max_live() { return A_MAX; }
 int bank_nc(int Tc, int spc) { return (Tc + 2 * spc - 2) / spc; }
 int bank_row_len(int Tc, int spc) { return spc * (bank_nc(Tc, spc) + 2 * PAD_CHUNKS); }
 
-int launch_bank(const BankParams &p_in, cudaStream_t st)
+static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
 {
     BankParams p = p_in;
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
@@ -579,17 +581,25 @@ int launch_bank(const BankParams &p_in, cudaStream_t st)
     CUtensorMap mc, mh, mc3, mh3;
     // tensor maps count 32-bit words: one int16 sample or two u8 samples
     const long n_words = (p.in.n * eb + 3) / 4, pitch_words = p.in.pitch * eb / 4, hist_words = (long)p.H * eb / 4;
-    if (!encode_rows(&mc, p.in.cur, n_words, p.n_streams, pitch_words) || !encode_rows(&mh, p.in.hist, hist_words, p.n_streams, hist_words) ||
-        !encode_rows3(&mc3, p.in.cur, p.in.n * eb / (BOX_SAMPLES * 4), p.n_streams, pitch_words) ||
-        !encode_rows3(&mh3, p.in.hist, hist_words / BOX_SAMPLES, p.n_streams, hist_words))
+    if (!encode_rows(&mc, p.in.cur, n_words, p.n_streams, pitch_words) ||
+        !encode_rows3(&mc3, p.in.cur, p.in.n * eb / (BOX_SAMPLES * 4), p.n_streams, pitch_words))
         return SFE_ERR_CUDA;
+    if (p.H == 0) {                          // no history rows (time-split launches): the maps are never used
+        mh = mc;
+        mh3 = mc3;
+    } else if (!encode_rows(&mh, p.in.hist, hist_words, p.n_streams, hist_words) ||
+               !encode_rows3(&mh3, p.in.hist, hist_words / BOX_SAMPLES, p.n_streams, hist_words)) {
+        return SFE_ERR_CUDA;
+    }
     int dev = 0, sms = 0;
     if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
     p.n_groups = (p.n_streams + BOX_ROWS - 1) / BOX_ROWS;
     // one work item per warp slot of the machine, but never fewer than 8 outputs per item
     // (rounded down: one item too many would cost a whole second wave)
     long n_seg = ((long)sms * v.warps) / p.n_groups;
-    if (n_seg > p.n_out / 8) n_seg = p.n_out / 8;
+    long cap = p.n_out / 8;
+    if (p.n_groups * cap < (long)sms * v.warps / 2) cap = p.n_out / 2;   // a small job: fill the machine first
+    if (n_seg > cap) n_seg = cap;
     if (n_seg < 1) n_seg = 1;
     p.n_seg = (int)n_seg;
     const long items = (long)p.n_groups * p.n_seg;
@@ -598,6 +608,72 @@ int launch_bank(const BankParams &p_in, cudaStream_t st)
     kern<<<(unsigned)((items + v.warps - 1) / v.warps), v.warps * 32, smem, st>>>(mc, mh, mc3, mh3, p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+}
+
+// A single stream (or a few) leaves 31 of the 32 lanes of every warp idle.  The bank is periodically time invariant, so
+// a long row can be cut into P pieces of Kp outputs each (Kp a multiple of the phase period L / gcd(step, L)) that all
+// follow the schedule of piece 0 shifted by Q = D Kp step / L samples: pieces 1..P-1 become the rows of a second launch
+// whose "current" samples start H samples before the piece (their history is simply the preceding part of the row),
+// and the outputs behind the last whole piece form a third, one-row launch.  Results are those of the unsplit launch
+// bit for bit (same windows, same taps, same summation order).
+static long gcd_l(long a, long b) { return b ? gcd_l(b, a % b) : a; }
+
+int launch_bank(const BankParams &p, cudaStream_t st)
+{
+    const int eb = fmt_bytes(p.in.fmt), spc = 16 / (eb > 0 ? eb : 4);
+    static const bool no_split = getenv("SFE_BANK_NO_SPLIT") != nullptr;
+    if (p.n_streams != 1 || p.n_out < 2048 || no_split || p.step <= 0) return launch_bank_rows(p, st);
+    const long sl = ((p.step % p.L) + p.L) % p.L;
+    const long period = p.L / gcd_l(sl ? sl : p.L, p.L);
+    // outputs per piece: whole periods, at least 16 outputs, and a piece length that keeps rows 16-byte aligned
+    long Kp = 0, Q = 0;
+    for (long m = (16 + period - 1) / period; m <= (16 + period - 1) / period + 4 * spc; m++) {
+        const long k = m * period;
+        const long q = (long)p.D * (k * p.step / p.L);
+        if ((k * p.step) % p.L == 0 && q % spc == 0 && q >= p.H) { Kp = k; Q = q; break; }
+    }
+    if (!Kp) return launch_bank_rows(p, st);
+    // samples a piece may touch behind its own Q: the offset of output 0 plus one window step
+    long M0 = p.pos0 / p.L;
+    if (p.pos0 - M0 * p.L < 0) M0 -= 1;
+    const long extra = std::max<long>(0, p.n_first + (long)p.D * M0) + (long)p.D * (p.step / p.L + 2) + 8 * spc;
+    long P = p.n_out / Kp;
+    while (P > 1 && P * Q + extra > p.in.n) P--;
+    if (P < 64) return launch_bank_rows(p, st);
+
+    BankParams a = p;                        // piece 0: the real history
+    a.n_out = Kp;
+    int rc = launch_bank_rows(a, st);
+    if (rc != SFE_OK) return rc;
+    BankParams b = p;                        // pieces 1..P-1 as rows
+    b.in.cur = static_cast<const char *>(p.in.cur) + (Q - p.H) * eb;
+    b.in.hist = b.in.cur;
+    b.in.pitch = Q;
+    b.in.H = 0;
+    b.in.n = Q + p.H + extra;
+    b.H = 0;
+    b.n_first = p.n_first + p.H;
+    b.n_streams = (int)(P - 1);
+    b.n_out = Kp;
+    b.out = p.out + Kp;
+    b.out_pitch = Kp;
+    rc = launch_bank_rows(b, st);
+    if (rc != SFE_OK) return rc;
+    if (p.n_out > P * Kp) {                  // the ragged end: one row from the end of the last whole piece
+        BankParams c = b;
+        c.in.cur = static_cast<const char *>(p.in.cur) + (P * Q - p.H) * eb;
+        c.in.hist = c.in.cur;
+        c.in.pitch = p.in.n - P * Q + p.H;
+        c.in.n = p.in.n - P * Q + p.H;
+        c.n_streams = 1;
+        c.n_out = p.n_out - P * Kp;
+        c.out = p.out + P * Kp;
+        c.out_pitch = c.n_out;
+        // a one-row tensor map still wants a 16-byte pitch
+        c.in.pitch = (c.in.pitch + spc - 1) / spc * spc;
+        rc = launch_bank_rows(c, st);
+    }
+    return rc;
 }
 
 // Host side: the bank table.  c_ph[u] = sum_j r[ph + L j] g[u - D j] in double, scaled, rounded to float, stored

@@ -429,3 +429,25 @@ def test_chain_generic_stage_fractional_rates(gpu_lib, oracle_lib, up, rate, tap
     assert got.shape == ref.shape, (got.shape, ref.shape)
     nrms, peak = F.err_metrics(got, ref)
     assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
+
+
+@pytest.mark.parametrize("base,N,fmt", [("cfg3_small", 2_000_001, F.IN_I16), ("cfg5_small", 600_001, F.IN_I16), ("cfg5_small", 900_003, F.IN_U8)])
+def test_chain_bank_single_stream_time_split(gpu_lib, oracle_lib, base, N, fmt):
+    """one long stream: the bank launch cuts the row into pieces that run as the rows of one launch (lanes would idle
+    otherwise).  Must equal the unsplit kernel bit for bit (same stream fed as two rows) and the oracle within tolerance;
+    fed in two ragged calls so that history, alignment and a held-over schedule cross the seam."""
+    from oracle import oracle as O
+    cfg = dict(F.CONFIGS[base], S=1, N=N, in_fmt=fmt)
+    iq = F.make_input(cfg)
+    ref, _ = O.chain_run(iq, fmt, cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib)
+    cut = N // 2 + 1237
+    one = _chain(cfg)
+    assert one.plan.startswith("bank_fused"), one.plan
+    got = np.concatenate([one.process(iq[:, :cut]), one.process(iq[:, cut:])], axis=1)
+    two = _chain(cfg, S=2)
+    iq2 = np.concatenate([iq, iq], axis=0)
+    dup = np.concatenate([two.process(iq2[:, :cut]), two.process(iq2[:, cut:])], axis=1)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    assert np.array_equal(got[0], dup[0]) and np.array_equal(dup[0], dup[1]), "time-split launch == row launch, bit for bit"
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
