@@ -81,11 +81,43 @@ def run_case(name, cfg, S, N, flags, steps, warmup, peak, torch, Chain):
     return res
 
 
+def cpu_table():
+    """the reference's CPU code (oracle/_ref, -O3) on every BASELINE config: one stream on one thread, and one
+    stream per thread on all host threads, on a bounded sample (<= 2^20 samples per stream)"""
+    import time
+    import numpy as np
+    from oracle import oracle as O
+    lib = O.load("auto", fast=True)
+    T = len(os.sched_getaffinity(0))
+    rows = []
+    for name in ("cfg1", "cfg2", "cfg3", "cfg4", "cfg5"):
+        cfg = dict(F.CONFIGS[name], S=1, N=min(F.CONFIGS[name]["N"], 1 << 20))
+        x1 = F.make_input(cfg)
+        xT = np.ascontiguousarray(np.repeat(x1, T, axis=0))
+        best1 = bestT = 1e30
+        for _ in range(3):
+            t0 = time.perf_counter()
+            O.chain_run(x1, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), n_threads=1, lib=lib)
+            best1 = min(best1, time.perf_counter() - t0)
+            t0 = time.perf_counter()
+            O.chain_run(xT, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), n_threads=T, lib=lib)
+            bestT = min(bestT, time.perf_counter() - t0)
+        rows.append({"config": name, "samples_per_stream": cfg["N"], "cpu_1thread_Msamples_per_s": cfg["N"] / best1 / 1e6,
+                     "cpu_all_threads_Msamples_per_s": T * cfg["N"] / bestT / 1e6, "threads": T,
+                     "kind": lib.sfeo_kind().decode(), "build": lib.sfeo_build_flags().decode()})
+        print(json.dumps(rows[-1]), file=sys.stderr, flush=True)
+    return rows
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--only", default="")
+    ap.add_argument("--cpu", action="store_true", help="only time the reference CPU code on every config")
     args = ap.parse_args()
+    if args.cpu:
+        print(json.dumps({"cpu": cpu_table()}, indent=1))
+        return
     import torch
     import simplefe_b200  # noqa: F401
     from simplefe_b200.chain import Chain

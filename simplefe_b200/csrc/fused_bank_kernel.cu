@@ -591,8 +591,22 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
                !encode_rows3(&mh3, p.in.hist, hist_words / BOX_SAMPLES, p.n_streams, hist_words)) {
         return SFE_ERR_CUDA;
     }
-    int dev = 0, sms = 0;
-    if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
+    int dev = 0;
+    if (!SFE_CUDA(cudaGetDevice(&dev))) return SFE_ERR_CUDA;
+    static std::mutex cache_mutex;
+    static std::map<int, int> sm_count;                                   // per device
+    static std::map<std::pair<int, const void *>, size_t> smem_set;      // (device, kernel) -> opted-in bytes
+    int sms = 0;
+    {
+        std::lock_guard<std::mutex> lk(cache_mutex);
+        auto it = sm_count.find(dev);
+        if (it == sm_count.end()) {
+            if (!SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
+            sm_count[dev] = sms;
+        } else {
+            sms = it->second;
+        }
+    }
     p.n_groups = (p.n_streams + BOX_ROWS - 1) / BOX_ROWS;
     // one work item per warp slot of the machine, but never fewer than 8 outputs per item
     // (rounded down: one item too many would cost a whole second wave)
@@ -604,7 +618,14 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
     p.n_seg = (int)n_seg;
     const long items = (long)p.n_groups * p.n_seg;
     const size_t smem = bank_smem_bytes(p.n_rows, p.row_len);
-    if (!SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
+    {
+        std::lock_guard<std::mutex> lk(cache_mutex);
+        size_t &have = smem_set[{dev, reinterpret_cast<const void *>(kern)}];
+        if (have < smem) {
+            if (!SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
+            have = smem;
+        }
+    }
     kern<<<(unsigned)((items + v.warps - 1) / v.warps), v.warps * 32, smem, st>>>(mc, mh, mc3, mh3, p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
