@@ -152,6 +152,10 @@ __global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepPar
         const bool aligned = ((X0 & 3) == 0) && ((p.in.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.in.cur) & 15) == 0);
         int p_slot = 0;
         uint32_t p_par = 0;
+        const uint32_t ring_sa = smem_u32(ring);
+        uint32_t soff[4];                                  // swizzled byte offsets of this thread's four plane rows (q = 0)
+#pragma unroll
+        for (int k = 0; k < 4; k++) soff[k] = swz(4 * pw + k, 4 * lane);
         PieceIter it(p);
         Piece pc;
         while (it.next(pc)) {
@@ -159,14 +163,26 @@ __global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepPar
             // The loads of step m + PF are issued before step m is split and stored: PF K-blocks (2 KB per warp each)
             // stay in flight per warp.  Without this a warp holds one step's loads at a time and the whole CTA moves
             // 16 KB per HBM round trip (measured 1.37 us per step; tensor pipe 7 % busy).
-            auto load_step = [&](long m, uint4 (&v)[4]) {
-                const long n0 = X0 + 128 * m + 4 * lane;   // this lane's 4 samples
+            // per piece: row pointers of this warp's four streams; per step only the sample offset moves
+            const uint32_t *rowp[4];
+            bool row_ok[4];
 #pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    const int sl = pw + 8 * q, s = s_base + sl;
-                    if (aligned && s < p.n_streams && n0 >= 0 && n0 + 3 < p.in.n) {
-                        v[q] = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const uint32_t *>(p.in.cur) + (long)s * p.in.pitch + n0));
-                    } else {
+            for (int q = 0; q < 4; q++) {
+                const int s = s_base + pw + 8 * q;
+                row_ok[q] = s < p.n_streams;
+                rowp[q] = reinterpret_cast<const uint32_t *>(p.in.cur) + (long)(row_ok[q] ? s : 0) * p.in.pitch;
+            }
+            auto load_step = [&](long m, uint4 (&v)[4]) {
+                const long nb = X0 + 128 * m;              // first sample of the K-block (warp uniform)
+                const long n0 = nb + 4 * lane;             // this lane's 4 samples
+                if (aligned && nb >= 0 && nb + 128 <= p.in.n) {   // whole block inside the current rows
+#pragma unroll
+                    for (int q = 0; q < 4; q++)
+                        v[q] = row_ok[q] ? __ldg(reinterpret_cast<const uint4 *>(rowp[q] + n0)) : make_uint4(0u, 0u, 0u, 0u);
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        const int s = s_base + pw + 8 * q;
                         v[q].x = load_i16(p, s, n0);
                         v[q].y = load_i16(p, s, n0 + 1);
                         v[q].z = load_i16(p, s, n0 + 2);
@@ -179,19 +195,18 @@ __global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepPar
                 const uint32_t par = p_par;
                 if (++p_slot == R) { p_slot = 0; p_par ^= 1; }
                 mbar_wait(&bar_empty[slot], par ^ 1);      // slot free (first pass falls through)
-                uint8_t *tile = ring + (size_t)slot * TILE_BYTES;
+                const uint32_t tile = ring_sa + (uint32_t)slot * TILE_BYTES;
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
-                    const int sl = pw + 8 * q;
                     const uint32_t t01 = __byte_perm(v[q].x, v[q].y, 0x5140), t23 = __byte_perm(v[q].z, v[q].w, 0x5140);
                     const uint32_t u01 = __byte_perm(v[q].x, v[q].y, 0x7362), u23 = __byte_perm(v[q].z, v[q].w, 0x7362);
                     const uint32_t il = __byte_perm(t01, t23, 0x5410), ih = __byte_perm(t01, t23, 0x7632) ^ 0x80808080u;
                     const uint32_t ql = __byte_perm(u01, u23, 0x5410), qh = __byte_perm(u01, u23, 0x7632) ^ 0x80808080u;
-                    const int r = 4 * sl;
-                    *reinterpret_cast<uint32_t *>(tile + swz(r + 0, 4 * lane)) = il;
-                    *reinterpret_cast<uint32_t *>(tile + swz(r + 1, 4 * lane)) = ih;
-                    *reinterpret_cast<uint32_t *>(tile + swz(r + 2, 4 * lane)) = ql;
-                    *reinterpret_cast<uint32_t *>(tile + swz(r + 3, 4 * lane)) = qh;
+                    // rows 4*(pw + 8q) + k: the swizzle term (row & 7) does not depend on q, tiles rows 32 apart are 4096 B apart
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[0] + q * 4096), "r"(il) : "memory");
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[1] + q * 4096), "r"(ih) : "memory");
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[2] + q * 4096), "r"(ql) : "memory");
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[3] + q * 4096), "r"(qh) : "memory");
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&bar_full[slot]);
@@ -216,6 +231,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepPar
         if (lane == 0) {
             const uint32_t idesc = (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t)(TNCOL >> 3) << 17) | ((128u >> 4) << 24);
             const uint32_t ring_a = smem_u32(ring), b_a = smem_u32(sB);
+            // umma_desc() split into its constant high word and the low word of tile 0 (address >> 4 | LBO = 1 at bit 16)
+            const uint32_t d_hi = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t a_lo0 = ((ring_a & 0x3FFFF) >> 4) | (1u << 16), b_lo0 = ((b_a & 0x3FFFF) >> 4) | (1u << 16);
             // ring bookkeeping in 32-bit increments: this one thread is the pacemaker of the CTA, and 64-bit
             // modulo/divide per K-block (software routines) cost it ~2700 cycles per step
             int ws = 0;                                    // slot / lap parity of the next K-block to wait for
@@ -235,18 +253,27 @@ __global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepPar
                     mbar_wait(&bar_acc_empty[a], ((step >> 1) & 1) ^ 1);
                     asm volatile("tcgen05.fence::after_thread_sync;");
                     const uint32_t d_tmem = tmem + a * ACC_STRIDE;
+                    // descriptors differ only in their 14-bit address field: one 32-bit add per operand and MMA
+                    uint32_t a_lo = a_lo0 + (uint32_t)hs * (TILE_BYTES >> 4), b_lo = b_lo0;
                     int slot = hs;
                     for (int kb = 0; kb < KB; kb++) {
-                        const uint32_t at = ring_a + slot * TILE_BYTES, bt = b_a + kb * (TNCOL * 128);
-                        if (++slot == R) slot = 0;
 #pragma unroll
                         for (int ks = 0; ks < 4; ks++) {
-                            const uint64_t da = umma_desc(at + ks * 32), db = umma_desc(bt + ks * 32);
-                            const uint32_t acc = (kb | ks) ? 1u : 0u;
-                            asm volatile("{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
-                                         " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n"
-                                         ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+                            uint64_t da, db;
+                            asm("mov.b64 %0, {%1, %2};" : "=l"(da) : "r"(a_lo + 2 * ks), "r"(d_hi));
+                            asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + 2 * ks), "r"(d_hi));
+                            if (ks == 0)
+                                asm volatile("{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+                                             " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n"
+                                             ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(kb) : "memory");
+                            else
+                                asm volatile("{\n .reg .pred p;\n setp.eq.b32 p, 0, 0;\n"
+                                             " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n"
+                                             ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc) : "memory");
                         }
+                        b_lo += (TNCOL * 128) >> 4;
+                        a_lo += TILE_BYTES >> 4;
+                        if (++slot == R) { slot = 0; a_lo = a_lo0; }
                     }
                     umma_commit(&bar_acc_full[a]);                                   // accumulator ready
                     umma_commit(&bar_empty[hs]);                                     // oldest K-block retired
@@ -264,8 +291,11 @@ __global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepPar
         // =================================== epilogue ================================================
         const int plane = lane & 3;                        // 0 I_lo, 1 I_hi, 2 Q_lo, 3 Q_hi
         const bool hi = plane & 1;
-        const float c0 = hi ? p.corr[0] : 0.f, c1 = hi ? p.corr[1] : 0.f, c2 = hi ? p.corr[2] : 0.f;
+        // y = sum_tau w_tau (A_tau - c_tau) * byte_w with the weights pre-scaled
         const float byte_w = hi ? 256.f : 1.f;
+        const float w0 = p.w[0] * byte_w, w1 = p.w[1] * byte_w, w2 = p.w[2] * byte_w;
+        // the bias of the hi planes (128 * sum of the digit's taps, an exact integer) is removed in int32, before conversion
+        const int ci0 = hi ? (int)p.corr[0] : 0, ci1 = hi ? (int)p.corr[1] : 0, ci2 = hi ? (int)p.corr[2] : 0;
         long step = 0;
         PieceIter it(p);
         Piece pc;
@@ -291,10 +321,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepPar
                 float2 *o = p.out + (long)s * p.out_pitch + j * TNO;
 #pragma unroll
                 for (int i = 0; i < TNO; i++) {
-                    float f = p.w[0] * ((float)(int)v[i] - c0);
-                    f = fmaf(p.w[1], (float)(int)v[TNO + i] - c1, f);
-                    f = fmaf(p.w[2], (float)(int)v[2 * TNO + i] - c2, f);
-                    f *= byte_w;
+                    float f = w0 * (float)((int)v[i] - ci0);
+                    f = fmaf(w1, (float)((int)v[TNO + i] - ci1), f);
+                    f = fmaf(w2, (float)((int)v[2 * TNO + i] - ci2), f);
                     f += __shfl_xor_sync(0xffffffffu, f, 1);             // lo + 256*hi
                     const float q = __shfl_down_sync(0xffffffffu, f, 2); // Q next to I
                     if (plane == 0 && s < p.n_streams && j * TNO + i < p.n_out) o[i] = make_float2(f, q);
