@@ -42,6 +42,28 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# stdout carries exactly one JSON line.  Libraries write there too (NCCL prints its version line from C), so file
+# descriptor 1 is pointed at stderr for the whole run and the line goes out through a private duplicate.
+_JSON_FD = None
+
+
+def capture_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 # ---------------------------------------------------------------------------------------------------
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
@@ -177,7 +199,7 @@ def run_reference(args, cfg, rank, world):
         "e2e": {"value": v, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(cfg, n_gpus, streams_per_gpu=None, scaling="weak"):
@@ -205,6 +227,7 @@ def main():
                     help="weak: every GPU runs the full 1024-stream shard (box = N x 1024 streams); "
                          "strong: the 1024 streams are split over the N GPUs")
     args = ap.parse_args()
+    capture_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     rank = int(os.environ.get("RANK", "0"))
@@ -363,7 +386,7 @@ def main():
         "dtype": "f32", "data": "synthetic", "config": dict(workload_config(cfg, n_ranks, S, args.scaling), plan=ch.plan, outputs_per_stream=n_out),
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if n_ranks > 1:
         dist.barrier()
         dist.destroy_process_group()
