@@ -423,6 +423,157 @@ template <int FMT> DecimKernel decim_pick(int D, int QLP)
     return decim_fir_kernel<FMT, 0, 0>;
 }
 
+// ---------------------------------------------------------------------------------------------
+// K2s: the generic polyphase stage when MANY streams share the filter (and therefore the schedule): lane = stream.
+// One CTA = 32 streams x p.kt consecutive outputs.  The span is staged transposed, xs[sample][stream] with a row pitch
+// of 33 words, so a warp reads one sample of its 32 streams as 256 contiguous bytes (conflict free whatever the rate;
+// the thread-per-output kernel pays 5 wavefronts per LDS.64 for its 2.5-sample lane stride).  Per output the two
+// interpolation points collapse into one tap set, warp uniform because mu is shared by the streams:
+//   out = sum_i c_i x[n_top - i],  c_i = mu t1[i] + (1 - mu) t0[i - d],  n_top = floor((pos + 1) / L), d = n_top - n0
+// computed once per output by the lanes, stored as (c, c) pairs and broadcast: 2 LDS.64 + 1 FFMA2 per tap and stream.
+// Outputs are staged too and leave as contiguous runs per stream.  Not for SFE_FLAG_EXACT (different rounding order).
+// ---------------------------------------------------------------------------------------------
+constexpr int LS_WARPS = 4, LS_NT = 32 * LS_WARPS, LS_PITCH = 33;
+constexpr int LS_KPW = 16, LS_KT = LS_WARPS * LS_KPW;   // outputs per warp and per CTA, at most
+
+template <int FMT> __device__ __forceinline__ float2 ls_cvt(typename DRaw<FMT>::type w);
+template <> __device__ __forceinline__ float2 ls_cvt<SFE_IN_I16>(uint32_t w) { return cvt_i16(w); }
+template <> __device__ __forceinline__ float2 ls_cvt<SFE_IN_U8>(uint16_t w) { return cvt_u8(w); }
+template <> __device__ __forceinline__ float2 ls_cvt<SFE_IN_F32>(f32x2 w)
+{
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(w));
+    return r;
+}
+
+template <int FMT>
+__global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
+{
+    typedef typename DRaw<FMT>::type RT;
+    extern __shared__ __align__(16) unsigned char ls_sm[];
+    const int J = p.jp;                                                    // taps per phase (padded to odd)
+    float *tp = reinterpret_cast<float *>(ls_sm);                          // [up][J] phase major
+    f32x2 *cb = reinterpret_cast<f32x2 *>(ls_sm + p.tap_bytes);            // [LS_WARPS][J + 1] combined taps (c, c)
+    float2 *xs = reinterpret_cast<float2 *>(cb + LS_WARPS * (J + 1));      // [span][LS_PITCH]; reused for the outputs
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    const long k0 = (long)blockIdx.x * p.kt;
+    const long k1 = min(k0 + (long)p.kt, p.n_out) - 1;
+    const int s0 = blockIdx.y * 32;
+    long pos_lo, pos_hi;
+    float mu_unused;
+    poly_sched(p, k0, pos_lo, mu_unused);
+    poly_sched(p, k1, pos_hi, mu_unused);
+    const long n_lo = floordiv(pos_lo, p.up) - (J - 1);
+    const long n_hi = floordiv(pos_hi + 1, p.up);
+    const int span = (int)(n_hi - n_lo + 1);
+    if (span > p.span_cap) {   // cannot happen with the launcher's sizing unless the schedule is wildly non-uniform
+        for (long k = k0 + warp; k <= k1; k += LS_WARPS) {
+            long pos;
+            float mu;
+            poly_sched(p, k, pos, mu);
+            if (s0 + lane < p.n_streams) {
+                const float2 a = poly_point<false, false>(p, s0 + lane, pos);
+                const float2 b = mu != 0.f ? poly_point<false, false>(p, s0 + lane, pos + 1) : make_float2(0.f, 0.f);
+                poly_store<false, false>(p, s0 + lane, k, a, b, mu, mu != 0.f);
+            }
+        }
+        return;
+    }
+    for (int i = threadIdx.x; i < p.up * J; i += LS_NT) {
+        const int ph = i / J, j = i - ph * J, m = ph + j * p.up;
+        tp[i] = m < p.n_taps ? __ldg(p.taps + m) : 0.f;
+    }
+    // ---- stage the span transposed: warp w takes rows w, w + 4, ...; lanes run along the samples ----
+    const bool interior = n_lo >= 0 && n_hi < p.in.n;
+    if (interior) {
+        // all 8 rows of the warp x 2 sample chunks per round: 16 independent loads in flight per lane
+        const RT *src[32 / LS_WARPS];
+#pragma unroll
+        for (int rr = 0; rr < 32 / LS_WARPS; rr++) {
+            const int s = min(s0 + warp + LS_WARPS * rr, p.n_streams - 1);   // rows past the end repeat the last stream (never stored)
+            src[rr] = reinterpret_cast<const RT *>(p.in.cur) + (long)s * p.in.pitch + n_lo;
+        }
+        for (int i0 = lane; i0 < span; i0 += 64) {
+            RT raw[2][32 / LS_WARPS];
+#pragma unroll
+            for (int u = 0; u < 2; u++)
+#pragma unroll
+                for (int rr = 0; rr < 32 / LS_WARPS; rr++) raw[u][rr] = i0 + 32 * u < span ? __ldg(src[rr] + i0 + 32 * u) : RT();
+#pragma unroll
+            for (int u = 0; u < 2; u++)
+#pragma unroll
+                for (int rr = 0; rr < 32 / LS_WARPS; rr++)
+                    if (i0 + 32 * u < span) xs[(i0 + 32 * u) * LS_PITCH + warp + LS_WARPS * rr] = ls_cvt<FMT>(raw[u][rr]);
+        }
+    } else {
+        for (int r = warp; r < 32; r += LS_WARPS) {
+            const int s = s0 + r;
+            for (int i = lane; i < span; i += 32)
+                xs[i * LS_PITCH + r] = s < p.n_streams ? load_sample(p.in, s, n_lo + i) : make_float2(0.f, 0.f);
+        }
+    }
+    __syncthreads();
+    // ---- compute: warp w takes outputs k0 + w, k0 + w + 4, ...; every lane its own stream ----
+    f32x2 res[LS_KPW];
+    f32x2 *cw = cb + warp * (J + 1);
+#pragma unroll
+    for (int q = 0; q < LS_KPW; q++) {
+        res[q] = 0ull;
+        const long k = k0 + warp + LS_WARPS * q;
+        if (k > k1) continue;                                              // warp uniform
+        long pos;
+        float mu;
+        poly_sched(p, k, pos, mu);
+        const long n0 = floordiv(pos, p.up);
+        const int ph0 = (int)(pos - n0 * p.up);
+        int ph1 = ph0 + 1, d = 0;
+        if (ph1 == p.up) { ph1 = 0; d = 1; }
+        const float *t0 = tp + ph0 * J, *t1 = tp + ph1 * J;
+        const float w0 = 1.0f - mu;
+        __syncwarp();                                                      // the previous output's readers are done
+        for (int i = lane; i < J + d; i += 32) {
+            const float a = i < J ? t1[i] : 0.f, b = (i - d >= 0 && i - d < J) ? t0[i - d] : 0.f;
+            const float c = mu != 0.f ? fmaf(mu, a, w0 * b) : b;           // mu == 0: exactly the taps of s(pos)
+            cw[i] = d_pack2(c, c);
+        }
+        __syncwarp();
+        const float2 *xp = xs + (int)(n0 + d - n_lo) * LS_PITCH + lane;    // x[n_top] of this lane's stream
+        f32x2 acc = 0ull, acc2 = 0ull;
+        const int nt = J + d;
+        int i = 0;
+        for (; i + 3 < nt; i += 4) {                                       // four taps per round, all loads first
+            const f32x2 c0 = cw[i], c1 = cw[i + 1], c2 = cw[i + 2], c3 = cw[i + 3];
+            const f32x2 x0 = *reinterpret_cast<const f32x2 *>(xp - i * LS_PITCH);
+            const f32x2 x1 = *reinterpret_cast<const f32x2 *>(xp - (i + 1) * LS_PITCH);
+            const f32x2 x2 = *reinterpret_cast<const f32x2 *>(xp - (i + 2) * LS_PITCH);
+            const f32x2 x3 = *reinterpret_cast<const f32x2 *>(xp - (i + 3) * LS_PITCH);
+            acc = d_ffma2(c0, x0, acc);
+            acc2 = d_ffma2(c1, x1, acc2);
+            acc = d_ffma2(c2, x2, acc);
+            acc2 = d_ffma2(c3, x3, acc2);
+        }
+        for (; i < nt; i++) acc = d_ffma2(cw[i], *reinterpret_cast<const f32x2 *>(xp - i * LS_PITCH), acc);
+        res[q] = d_fadd2(acc, acc2);
+    }
+    __syncthreads();                                                       // all reads of xs are done: reuse it
+    f32x2 *ob = reinterpret_cast<f32x2 *>(xs);                             // [32 streams][kt + 1]
+    const int opitch = p.kt + 1;
+#pragma unroll
+    for (int q = 0; q < LS_KPW; q++) {
+        const int kl = warp + LS_WARPS * q;
+        if (k0 + kl <= k1) ob[lane * opitch + kl] = res[q];
+    }
+    __syncthreads();
+    const int nk = (int)(k1 - k0 + 1);
+    for (int r = warp; r < 32; r += LS_WARPS) {
+        const int s = s0 + r;
+        if (s >= p.n_streams) continue;
+        f32x2 *o = reinterpret_cast<f32x2 *>(p.out) + (long)s * p.out_pitch + k0;
+        for (int kl = lane; kl < nk; kl += 32) o[kl] = ob[r * opitch + kl];
+    }
+}
+
 }  // namespace
 
 int launch_poly_generic(const PolyParams &p_in, cudaStream_t st)
@@ -437,6 +588,28 @@ int launch_poly_generic(const PolyParams &p_in, cudaStream_t st)
     double step = p.uniform ? (double)p.step : 0.0;                        // grid positions per output
     if (!p.uniform) step = (double)p.rate * p.up;
     const double per_out = step / p.up;                                    // input samples per output
+    // many streams sharing the schedule: lane-per-stream flavour (K2s)
+    static const bool no_lanes = getenv("SFE_POLY_NO_LANES") != nullptr;   // tuning hook
+    if (!p.exact && !p.in_real && p.n_streams >= 16 && tap_bytes <= 32 * 1024 && !no_lanes) {
+        const long cap_s = (64 * 1024) / (LS_PITCH * 8);                   // samples of span per CTA
+        long kl = (long)((double)(cap_s - p.jp - 8) / (per_out * 1.01 + 1e-9));
+        if (kl > LS_KT) kl = LS_KT;
+        kl = kl / LS_WARPS * LS_WARPS;
+        if (kl >= 8) {
+            p.kt = (int)kl;
+            p.tap_bytes = (int)tap_bytes;
+            p.span_cap = (int)std::min<long>(cap_s, (long)((double)kl * per_out * 1.01) + p.jp + 8);
+            const size_t body = std::max<size_t>((size_t)p.span_cap * LS_PITCH * 8, (size_t)32 * (kl + 1) * 8);
+            const size_t smem_l = tap_bytes + (size_t)LS_WARPS * (p.jp + 1) * 8 + body;
+            auto kl_kern = p.in.fmt == SFE_IN_I16 ? poly_lanes_kernel<SFE_IN_I16> : p.in.fmt == SFE_IN_U8 ? poly_lanes_kernel<SFE_IN_U8> : poly_lanes_kernel<SFE_IN_F32>;
+            if (smem_l > 48 * 1024 && !SFE_CUDA(cudaFuncSetAttribute(kl_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l)))
+                return SFE_ERR_CUDA;
+            dim3 grid((unsigned)((p.n_out + kl - 1) / kl), (unsigned)((p.n_streams + 31) / 32));
+            kl_kern<<<grid, LS_NT, smem_l, st>>>(p);
+            count_launch();
+            return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+        }
+    }
     const long cap = POLY_SPAN_BYTES / eb;
     long kt = (long)((double)(cap - p.jp - 8) / (per_out * 1.01 + 1e-9));
     kt = kt / POLY_NT * POLY_NT;

@@ -451,3 +451,38 @@ def test_chain_bank_single_stream_time_split(gpu_lib, oracle_lib, base, N, fmt):
     assert np.array_equal(got[0], dup[0]) and np.array_equal(dup[0], dup[1]), "time-split launch == row launch, bit for bit"
     nrms, peak = F.err_metrics(got, ref)
     assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
+
+
+@pytest.mark.parametrize("up,rate,tapname,S,N,fmt", [(1, 2.5003, "taps31", 40, 40001, F.IN_F32), (4, 1.77, "taps31", 33, 20001, F.IN_I16),
+                                                      (3, 57.31, "rs512_l3", 17, 150001, F.IN_I16), (4, 0.77, "taps31", 35, 5001, F.IN_U8),
+                                                      (24, 26.7, "rs512_l24", 64, 60001, F.IN_I16)])
+def test_chain_generic_stage_many_streams(gpu_lib, oracle_lib, up, rate, tapname, S, N, fmt):
+    """>= 16 streams sharing a fractional-rate filter run the lane-per-stream kernel (K2s): ragged last group,
+    two calls (history, held-over output across the seam), decimation and interpolation"""
+    from oracle import oracle as O
+    klass = F.KLASS_RESAMPLE if rate < 1.0 else F.KLASS_DECIMATE
+    st = dict(klass=klass, taps=F.taps(tapname), up=up, blk=4096, rate=rate)
+    cfg = dict(in_fmt=fmt, S=S, N=N, seed=91, stage_a=st)
+    iq = F.make_input(cfg)
+    ch = _chain(cfg)
+    assert "polyphase_generic" in ch.plan
+    cut = (N // 3) // 4096 * 4096 + 4096
+    got = np.concatenate([ch.process(iq[:, :cut]), ch.process(iq[:, cut:])], axis=1)
+    ref, _ = O.chain_run(iq, fmt, None, st, None, lib=oracle_lib, n_threads=4)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    for s in range(S):
+        nrms, peak = F.err_metrics(got[s], ref[s])
+        assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (s, ch.plan, nrms, peak)
+
+
+def test_chain_cfg4_many_streams(gpu_lib, oracle_lib):
+    """the BPSK receive chain (FFT blkconv -> fractional decimate -> fractional resample) on 33 streams"""
+    from oracle import oracle as O
+    cfg = dict(F.CONFIGS["cfg4_small"], S=33, N=30000)
+    iq = F.make_input(cfg)
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=4)
+    got = _chain(cfg).process(iq)
+    assert got.shape == ref.shape
+    for s in range(33):
+        nrms, peak = F.err_metrics(got[s], ref[s])
+        assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (s, nrms, peak)
