@@ -19,6 +19,9 @@
 #include <cstdlib>
 #include <vector>
 
+#ifndef SFE_FFT_PACKED
+#define SFE_FFT_PACKED 1
+#endif
 #include "sfe_fft.cuh"
 #include "kernels.h"
 
@@ -131,7 +134,8 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
 #pragma unroll
             for (int k = 0; k < R; k++) v[k] = X[phi(b + j + k * S)];
         }
-        dft_dif<R, -1>(v);
+        if (SFE_FFT_PACKED) dft_dif_packed<R, -1>(v);
+        else dft_dif<R, -1>(v);
 #pragma unroll
         for (int sl = 0; sl < R; sl++) {
             constexpr int dummy = 0;
@@ -162,7 +166,8 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
             if (S > 1 && q != 0) y = cmul_conj(y, __ldg(c.p.tw + PL::tw_off(P) + (q - 1) * S + j));
             v[q] = y;
         }
-        dft_dif<R, +1>(v);
+        if (SFE_FFT_PACKED) dft_dif_packed<R, +1>(v);
+        else dft_dif<R, +1>(v);
 #pragma unroll
         for (int sl = 0; sl < R; sl++) {
             const int k = brev<R>(sl);

@@ -85,4 +85,68 @@ template <int R, int SIGN> __device__ __forceinline__ void dft_dif(float2 (&v)[R
     dif_stages<R, SIGN, R / 2>::run(v);
 }
 
+// ---- packed flavour: a complex value is one 64-bit register pair, so the butterfly's add and subtract are one
+// FADD2 each (sm_100 f32x2); twiddles work on the unpacked halves (a register pair aliases its two floats).
+typedef unsigned long long cpx2;
+__device__ __forceinline__ cpx2 cpack(float2 a)
+{
+    cpx2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a.x), "f"(a.y));
+    return r;
+}
+__device__ __forceinline__ float2 cunpack(cpx2 v)
+{
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+__device__ __forceinline__ cpx2 cadd2(cpx2 a, cpx2 b)
+{
+    cpx2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ cpx2 csub2(cpx2 a, cpx2 b)
+{
+    cpx2 d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+template <int R, int SIGN, int HALF, int G, int I> struct dif2_inner {
+    static __device__ __forceinline__ void run(cpx2 (&v)[R])
+    {
+        const cpx2 a = v[G + I], b = v[G + I + HALF];
+        v[G + I] = cadd2(a, b);
+        const cpx2 d = csub2(a, b);
+        constexpr int M16 = (I * 8) / HALF;
+        v[G + I + HALF] = M16 == 0 ? d : cpack(mul_w16<M16, SIGN>(cunpack(d)));
+        if constexpr (I + 1 < HALF) dif2_inner<R, SIGN, HALF, G, I + 1>::run(v);
+    }
+};
+template <int R, int SIGN, int HALF, int G> struct dif2_groups {
+    static __device__ __forceinline__ void run(cpx2 (&v)[R])
+    {
+        dif2_inner<R, SIGN, HALF, G, 0>::run(v);
+        if constexpr (G + 2 * HALF < R) dif2_groups<R, SIGN, HALF, G + 2 * HALF>::run(v);
+    }
+};
+template <int R, int SIGN, int HALF> struct dif2_stages {
+    static __device__ __forceinline__ void run(cpx2 (&v)[R])
+    {
+        dif2_groups<R, SIGN, HALF, 0>::run(v);
+        if constexpr (HALF > 1) dif2_stages<R, SIGN, HALF / 2>::run(v);
+    }
+};
+// same contract as dft_dif (natural order in, frequency q in slot brev<R>(q))
+template <int R, int SIGN> __device__ __forceinline__ void dft_dif_packed(float2 (&v)[R])
+{
+    cpx2 pv[R];
+#pragma unroll
+    for (int k = 0; k < R; k++) pv[k] = cpack(v[k]);
+    dif2_stages<R, SIGN, R / 2>::run(pv);
+#pragma unroll
+    for (int k = 0; k < R; k++) v[k] = cunpack(pv[k]);
+}
+
 }  // namespace sfe
