@@ -49,6 +49,9 @@ struct Op {
     Schedule sched;
     SchedEntry *d_sched = nullptr;
     size_t d_sched_cap = 0;
+    SchedEntry *h_sched = nullptr;   // pinned staging copy of the schedule
+    size_t h_sched_cap = 0;
+    cudaEvent_t h_sched_done = nullptr;
     // decimating FIR
     int D = 0, QLP = 0;
     float *d_gp = nullptr;
@@ -379,8 +382,24 @@ int upload_schedules(sfe_chain *c, cudaStream_t st)
             if (!SFE_CUDA(cudaMalloc(&op.d_sched, need * 2))) return SFE_ERR_CUDA;
             op.d_sched_cap = need * 2;
         }
-        // pageable source: the runtime stages the copy before returning, so the vector may be reused
-        if (!SFE_CUDA(cudaMemcpyAsync(op.d_sched, op.sched.e.data(), need, cudaMemcpyHostToDevice, st))) return SFE_ERR_CUDA;
+        // through a pinned staging buffer: the copy is a real asynchronous DMA instead of a staged pageable one.  The
+        // buffer may only be rewritten once its previous copy has completed.
+        if (op.h_sched_cap < need) {
+            if (op.h_sched) {
+                cudaEventSynchronize(op.h_sched_done);
+                cudaFreeHost(op.h_sched);
+            }
+            op.h_sched = nullptr;
+            op.h_sched_cap = 0;
+            if (!SFE_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&op.h_sched), need * 2, cudaHostAllocDefault))) return SFE_ERR_CUDA;
+            op.h_sched_cap = need * 2;
+        }
+        if (!op.h_sched_done && !SFE_CUDA(cudaEventCreateWithFlags(&op.h_sched_done, cudaEventDisableTiming))) return SFE_ERR_CUDA;
+        if (!SFE_CUDA(cudaEventSynchronize(op.h_sched_done))) return SFE_ERR_CUDA;
+        memcpy(op.h_sched, op.sched.e.data(), need);
+        if (!SFE_CUDA(cudaMemcpyAsync(op.d_sched, op.h_sched, need, cudaMemcpyHostToDevice, st)) ||
+            !SFE_CUDA(cudaEventRecord(op.h_sched_done, st)))
+            return SFE_ERR_CUDA;
     }
     return SFE_OK;
 }
@@ -573,6 +592,8 @@ extern "C" void sfe_chain_destroy(sfe_chain *c)
         cudaFree(op.d_gp);
         cudaFree(op.d_bmat);
         cudaFree(op.d_sched);
+        if (op.h_sched) cudaFreeHost(op.h_sched);
+        if (op.h_sched_done) cudaEventDestroy(op.h_sched_done);
         for (auto &kv : op.d_tables) cudaFree(kv.second);
     }
     for (Workspace &w : c->ws) {
