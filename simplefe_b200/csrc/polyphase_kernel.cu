@@ -98,10 +98,13 @@ __device__ __forceinline__ void poly_sched(const PolyParams &p, long k, long &po
     }
 }
 
+// grid positions of one call fit 32 bits (SchedEntry::pos is an int32): 32-bit division, not the 64-bit software routine
 __device__ __forceinline__ long floordiv(long a, int b)
 {
-    long q = a / b;
-    if (a - q * b < 0) q -= 1;
+    const int ai = (int)a;
+    if (b == 1) return ai;
+    int q = ai / b;
+    if (ai - q * b < 0) q -= 1;
     return q;
 }
 
