@@ -66,8 +66,10 @@ def emit(line: dict):
 
 # ---------------------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe).  The sampler is started
+    early (nvidia-smi needs ~0.1-0.3 s before its first line) and every line carries a timestamp, so samples are
+    attributed to the window they were taken in."""
+    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index: int):
@@ -80,37 +82,45 @@ class ClockSampler:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.gpu), "-lms", "100"], stdout=open(self.path, "w"),
+                                          "-i", str(self.gpu), "-lms", "20"], stdout=open(self.path, "w"),
                                          stderr=subprocess.DEVNULL)
+            t0 = time.time()
+            while time.time() - t0 < 3.0 and os.path.getsize(self.path) == 0:   # wait for the first line
+                time.sleep(0.02)
         except Exception:
             self.proc = None
 
-    def stop(self) -> dict:
+    def stop(self, t_lo: float, t_hi: float) -> dict:
+        """summary of the samples whose timestamp lies in [t_lo, t_hi] (time.time() seconds)"""
+        import datetime
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, mx, pw, reasons = [], [], [], set()
+        sm, mx, pw, reasons, n_all = [], [], [], set(), 0
         for line in open(self.path):
             f = [x.strip() for x in line.split(",")]
-            if len(f) < 9:
+            if len(f) < 10:
                 continue
+            n_all += 1
             try:
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
-                pw.append(float(f[3]))
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                if ts < t_lo - 0.011 or ts > t_hi + 0.011:
+                    continue
+                sm.append(float(f[2]))
+                mx.append(float(f[3]))
+                pw.append(float(f[4]))
             except ValueError:
                 continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[6:10]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         os.unlink(self.path)
         if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"], "samples_total": n_all}
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
                 "samples": len(sm), "reasons": sorted(reasons)}
 
@@ -300,14 +310,29 @@ def main():
     launches0 = lib.sfe_kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    w0 = time.time()
     e0.record(stream)
     for _ in range(args.steps):
         n_out = step()
     e1.record(stream)
     barrier()
+    w1 = time.time()
     ms = e0.elapsed_time(e1)
     launches = lib.sfe_kernel_launches() - launches0
-    clocks = sampler.stop() if rank == 0 else None
+    ch.profile(False)
+    # K steps of 0.7 ms are shorter than one nvidia-smi period: the same loop keeps running, untimed, until the
+    # sampler has seen at least 0.25 s of this load; the clocks line covers the timed region plus that continuation
+    w2 = w1
+    if rank == 0:
+        while time.time() - w0 < 0.25:
+            for _ in range(20):
+                step()
+            torch.cuda.synchronize()
+        w2 = time.time()
+    clocks = sampler.stop(w0, w2) if rank == 0 else None
+    if clocks is not None:
+        clocks["window"] = f"timed region ({(w1 - w0) * 1e3:.1f} ms) + untimed continuation of the same loop to {(w2 - w0) * 1e3:.0f} ms"
+    barrier()
     ch.profile(False)
     prof = ch.profile_read()
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
