@@ -22,6 +22,8 @@
 //   warps 5-12 producers  128-bit global loads of int16 IQ, byte-plane split with PRMT, stores into the
 //                         K-major SWIZZLE_128B operand tiles of a shared-memory ring (no im2col copy:
 //                         consecutive steps reuse KB-1 of their KB K-block tiles)
+#include <cstdlib>
+
 #include "kernels.h"
 
 namespace sfe {
@@ -36,7 +38,7 @@ constexpr int TILE_BYTES = 128 * 128;
 constexpr int N_EPI_WARPS = 4, N_PROD_WARPS = 8;
 constexpr int N_THREADS = 32 * (N_EPI_WARPS + 1 + N_PROD_WARPS);
 constexpr int MAX_RING = 12;
-constexpr int TPF = 3;              // producer prefetch depth (K-blocks in flight per warp)
+constexpr int TPF = 2;              // producer prefetch depth (K-blocks in flight per warp)
 constexpr int ACC_STRIDE = 64;     // TMEM columns between the two accumulators
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -108,7 +110,7 @@ __device__ __forceinline__ uint32_t load_i16(const ToepParams &p, int s, long n)
     return h < 0 ? 0u : __ldg(reinterpret_cast<const uint32_t *>(p.in.hist) + (long)s * p.in.H + h);
 }
 
-__global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepParams p)
+__global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const ToepParams p)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bar_full[MAX_RING], bar_empty[MAX_RING], bar_acc_full[2], bar_acc_empty[2];
@@ -305,28 +307,31 @@ __global__ void __launch_bounds__(N_THREADS, 1) toeplitz_i8_kernel(const ToepPar
                 const int a = (int)(step & 1);
                 mbar_wait(&bar_acc_full[a], (uint32_t)((step >> 1) & 1));
                 asm volatile("tcgen05.fence::after_thread_sync;");
-                uint32_t v[TNCOL];
+                // one digit (16 columns) at a time: 16 + 16 live registers instead of 48 + 16, so that two CTAs fit an SM
+                float f[TNO];
                 const uint32_t ta = tmem + ((uint32_t)(warp * 32) << 16) + a * ACC_STRIDE;
 #pragma unroll
-                for (int c = 0; c < TNT; c++)
+                for (int c = 0; c < TNT; c++) {
+                    uint32_t v[16];
                     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                                 : "=r"(v[16 * c + 0]), "=r"(v[16 * c + 1]), "=r"(v[16 * c + 2]), "=r"(v[16 * c + 3]), "=r"(v[16 * c + 4]),
-                                   "=r"(v[16 * c + 5]), "=r"(v[16 * c + 6]), "=r"(v[16 * c + 7]), "=r"(v[16 * c + 8]), "=r"(v[16 * c + 9]),
-                                   "=r"(v[16 * c + 10]), "=r"(v[16 * c + 11]), "=r"(v[16 * c + 12]), "=r"(v[16 * c + 13]),
-                                   "=r"(v[16 * c + 14]), "=r"(v[16 * c + 15])
+                                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+                                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                                  : "r"(ta + 16 * c));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const float wc = c == 0 ? w0 : c == 1 ? w1 : w2;
+                    const int cc = c == 0 ? ci0 : c == 1 ? ci1 : ci2;
+#pragma unroll
+                    for (int i = 0; i < TNO; i++) f[i] = c == 0 ? wc * (float)((int)v[i] - cc) : fmaf(wc, (float)((int)v[i] - cc), f[i]);
+                }
                 asm volatile("tcgen05.fence::before_thread_sync;");
                 mbar_arrive(&bar_acc_empty[a]);            // TMEM buffer free for the step after next
                 float2 *o = p.out + (long)s * p.out_pitch + j * TNO;
 #pragma unroll
                 for (int i = 0; i < TNO; i++) {
-                    float f = w0 * (float)((int)v[i] - ci0);
-                    f = fmaf(w1, (float)((int)v[TNO + i] - ci1), f);
-                    f = fmaf(w2, (float)((int)v[2 * TNO + i] - ci2), f);
-                    f += __shfl_xor_sync(0xffffffffu, f, 1);             // lo + 256*hi
-                    const float q = __shfl_down_sync(0xffffffffu, f, 2); // Q next to I
-                    if (plane == 0 && s < p.n_streams && j * TNO + i < p.n_out) o[i] = make_float2(f, q);
+                    float fi = f[i];
+                    fi += __shfl_xor_sync(0xffffffffu, fi, 1);             // lo + 256*hi
+                    const float q = __shfl_down_sync(0xffffffffu, fi, 2); // Q next to I
+                    if (plane == 0 && s < p.n_streams && j * TNO + i < p.n_out) o[i] = make_float2(fi, q);
                 }
             }
         }
@@ -359,7 +364,11 @@ int launch_toeplitz(const ToepParams &p_in, cudaStream_t st)
     if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
     const long F = (long)p.n_groups * p.n_steps;
     long grid = F / 4 > 0 ? F / 4 : 1;                    // at least ~4 steps per CTA
-    if (grid > sms) grid = sms;
+    // two CTAs per SM when their rings fit (72 registers x 416 threads and 128 TMEM columns each): the second CTA's warps
+    // fill the issue slots the first one leaves while its producers, MMA thread and epilogue wait on each other
+    static const bool one_cta = getenv("SFE_TOEP_ONE_CTA") != nullptr;   // tuning hook
+    const int per_sm = (2 * (smem + 2048) <= 227 * 1024 && !one_cta) ? 2 : 1;
+    if (grid > (long)sms * per_sm) grid = (long)sms * per_sm;
     toeplitz_i8_kernel<<<(unsigned)grid, N_THREADS, smem, st>>>(p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
