@@ -23,16 +23,6 @@ constexpr int POLY_SPAN_BYTES = 32 * 1024;   // staged input span per CTA
 // K2g: any L, any rate, table or closed-form schedule, complex or real rows.  poly_point is the direct
 // form (window read straight from global memory), used for tiles too sparse to stage.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float2 load_real(const StreamView &v, int s, long n)   // float rows (single-object API)
-{
-    float xr = 0.f;
-    if (n < v.n) {
-        if (n >= 0) xr = __ldg(reinterpret_cast<const float *>(v.cur) + (long)s * v.pitch + n);
-        else if (v.H + n >= 0) xr = __ldg(reinterpret_cast<const float *>(v.hist) + (long)s * v.H + v.H + n);
-    }
-    return make_float2(xr, 0.f);
-}
-
 template <bool EXACT, bool REAL>
 __device__ __forceinline__ float2 poly_point(const PolyParams &p, int s, long pos)
 {

@@ -63,12 +63,8 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar)
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// K-major SWIZZLE_128B operand tile: rows 128 B apart, 8-row groups 1024 B apart (SBO), descriptor version 1
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr)
-{
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
-           ((uint64_t)2 << 61);
-}
+// Operand tiles are K-major SWIZZLE_128B: rows 128 B apart, 8-row groups 1024 B apart (SBO), descriptor version 1;
+// the MMA issuer builds the 64-bit descriptors from a constant high word and a 14-bit address field (see there).
 __device__ __forceinline__ uint32_t swz(int row, int byte)  // byte offset inside a tile
 {
     return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((byte >> 4) ^ (row & 7)) << 4) | (byte & 15)));
