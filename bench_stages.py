@@ -109,6 +109,41 @@ def cpu_table():
     return rows
 
 
+def tx_cases(peak, torch):
+    """batched BPSK transmitter: bits -> RRC interpolator -> float samples / 10-bit DAC words.
+    Unit: output samples; algorithmic bytes = bits read + samples written."""
+    from simplefe_b200 import bpsk as B
+    out = []
+    C, n_sym, sps = 1024, 1 << 17, 10
+    dev = torch.device("cuda", 0)
+    words = torch.randint(0, 2 ** 31 - 1, (C, n_sym // 32), dtype=torch.int32, device=dev)
+    for name, fmt, bps in (("float32 samples", B.TX_F32, 4.0), ("10-bit DAC words (5 bytes per 4 samples)", B.TX_DAC10, 1.25)):
+        tx = B.BpskTx(F.taps("rrc111"), sps, C)
+        d_out = torch.empty((C, int(n_sym * sps * bps)), dtype=torch.uint8, device=dev)
+        st = torch.cuda.current_stream()
+
+        def step():
+            tx.process_dev(words.data_ptr(), n_sym, n_sym // 32, d_out.data_ptr(), d_out.shape[1], fmt, st.cuda_stream)
+
+        for _ in range(3):
+            step()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(10):
+            step()
+        e1.record(st)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        n = C * n_sym * sps
+        b = C * n_sym / 8 + n * bps
+        out.append({"case": f"bpsk tx x{C} channels, 111-tap RRC, {sps} samples/symbol -> {name}", "channels": C, "symbols_per_channel": n_sym,
+                    "ms_per_step": ms, "Msamples_per_s": n / ms / 1e3, "bytes_alg_per_sample": b / n, "alg_GBps": b / ms / 1e6,
+                    "frac_of_measured_hbm": b / ms / 1e6 / peak})
+        print(json.dumps(out[-1]), file=sys.stderr, flush=True)
+        del tx, d_out
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
@@ -157,6 +192,11 @@ def main():
             r = {"case": name, "error": repr(ex)}
         out.append(r)
         print(json.dumps(r), file=sys.stderr, flush=True)
+    if not args.only or "tx" in args.only:
+        try:
+            out.extend(tx_cases(peak, torch))
+        except Exception as ex:
+            out.append({"case": "bpsk tx", "error": repr(ex)})
     print(json.dumps({"hbm_peak_GBps": peak, "cases": out}, indent=1))
 
 

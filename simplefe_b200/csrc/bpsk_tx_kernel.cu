@@ -45,6 +45,7 @@ __device__ __forceinline__ uint64_t bits_window(const uint32_t *cur, uint64_t hi
     return w;
 }
 
+template <int MT>     // taps per phase, rounded up (the padding taps are zero)
 __global__ void __launch_bounds__(TX_THREADS)
 bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int n_hist, long n_sym, int sps, const float *taps,
                int n_taps, float amp, int out_dac10, void *out, long out_pitch_bytes)
@@ -59,27 +60,39 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
 
     for (int item = threadIdx.x; item < n_items; item += TX_THREADS) {
         const int r = item % sps, grp = item / sps;
-        float h[TX_MAXM];
-#pragma unroll
-        for (int m = 0; m < TX_MAXM; m++) h[m] = (m < M && r + m * sps < n_taps) ? __ldg(taps + r + m * sps) : 0.f;
         const long s_first = s0 + (long)grp * TX_GROUP;
         // window: bit 63 = symbol s_first + 15, ..., bit 0 = symbol s_first - 48
         const uint64_t w = bits_window(cur, hw, s_first + TX_GROUP - 1, n_sym);
+        float acc[TX_GROUP];
 #pragma unroll
-        for (int i = 0; i < TX_GROUP; i++) {
-            const long s = s_first + i;
-            float acc = 0.f;
+        for (int i = 0; i < TX_GROUP; i++) acc[i] = 0.f;
+        if (s_first - (M - 1) >= -(long)n_hist && s_first + TX_GROUP <= n_sym) {
+            // every symbol the group touches exists: the +-A impulse (bpsk.cxx:150) times the tap is the pre-scaled tap
+            // with its sign bit flipped by the symbol bit -- a shift, one LOP3 and one FADD per tap and output
 #pragma unroll
-            for (int m = 0; m < TX_MAXM; m++) {
-                if (m < M) {
-                    const int bit = 63 - (TX_GROUP - 1 - i) - m;           // symbol s - m
-                    const bool valid = (s - m) >= -(long)n_hist && s - m < n_sym;  // before the first symbol: zero state
-                    const float a = ((w >> bit) & 1ull) ? -amp : amp;      // bpsk.cxx:150
-                    acc = fmaf(valid ? a : 0.f, h[m], acc);
+            for (int m = 0; m < MT; m++) {
+                const uint32_t hb = __float_as_uint((m < M && r + m * sps < n_taps) ? amp * __ldg(taps + r + m * sps) : 0.f);
+                const uint32_t x = (uint32_t)(w >> (48 - m));              // bit i = symbol s_first + i - m
+#pragma unroll
+                for (int i = 0; i < TX_GROUP; i++)
+                    acc[i] += __uint_as_float(hb ^ ((x << (31 - i)) & 0x80000000u));
+            }
+        } else {
+            // first symbols of a stream (zero state before the history) and the ragged end
+            // (same arithmetic as above, tap by tap, so that a stream cut into calls anywhere gives identical samples)
+            for (int m = 0; m < M; m++) {
+                const uint32_t hb = __float_as_uint(r + m * sps < n_taps ? amp * __ldg(taps + r + m * sps) : 0.f);
+#pragma unroll
+                for (int i = 0; i < TX_GROUP; i++) {
+                    const long sm = s_first + i - m;                       // symbol s - m
+                    const bool valid = sm >= -(long)n_hist && sm < n_sym;  // before the first symbol: zero state
+                    const uint32_t sign = (uint32_t)((w >> (48 + i - m)) & 1ull) << 31;   // a set bit sends -A (bpsk.cxx:150)
+                    acc[i] += valid ? __uint_as_float(hb ^ sign) : 0.f;
                 }
             }
-            tile[(grp * TX_GROUP + i) * sps + r] = acc;
         }
+#pragma unroll
+        for (int i = 0; i < TX_GROUP; i++) tile[(grp * TX_GROUP + i) * sps + r] = acc[i];
     }
     __syncthreads();
 
@@ -147,10 +160,12 @@ int launch_bpsk_tx(const uint32_t *bits, long pitch_words, const uint64_t *hist_
 {
     if (n_sym <= 0 || n_channels <= 0) return SFE_OK;
     const size_t smem = sizeof(float) * TX_SYM * sps + (size_t)TX_SYM * sps / 4 * 5 + 16;
-    if (!SFE_CUDA(cudaFuncSetAttribute(bpsk_tx_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
+    const int M = (n_taps + sps - 1) / sps;
+    auto kern = M <= 4 ? bpsk_tx_kernel<4> : M <= 8 ? bpsk_tx_kernel<8> : M <= 12 ? bpsk_tx_kernel<12> : M <= 16 ? bpsk_tx_kernel<16>
+                : M <= 24 ? bpsk_tx_kernel<24> : bpsk_tx_kernel<32>;
+    if (!SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
     dim3 grid((unsigned)((n_sym + TX_SYM - 1) / TX_SYM), (unsigned)n_channels);
-    bpsk_tx_kernel<<<grid, TX_THREADS, smem, st>>>(bits, pitch_words, hist_old, n_hist, n_sym, sps, taps, n_taps, amp, out_dac10, out,
-                                                   out_pitch_bytes);
+    kern<<<grid, TX_THREADS, smem, st>>>(bits, pitch_words, hist_old, n_hist, n_sym, sps, taps, n_taps, amp, out_dac10, out, out_pitch_bytes);
     bpsk_tx_hist_kernel<<<(n_channels + 127) / 128, 128, 0, st>>>(bits, pitch_words, hist_old, hist_new, n_sym, n_channels);
     count_launch(2);
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
