@@ -67,15 +67,18 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
 #pragma unroll
         for (int i = 0; i < TX_GROUP; i++) acc[i] = 0.f;
         if (s_first - (M - 1) >= -(long)n_hist && s_first + TX_GROUP <= n_sym) {
-            // every symbol the group touches exists: the +-A impulse (bpsk.cxx:150) times the tap is the pre-scaled tap
-            // with its sign bit flipped by the symbol bit -- a shift, one LOP3 and one FADD per tap and output
+            // every symbol the group touches exists.  The +-A impulse (bpsk.cxx:150) times a tap is the pre-scaled tap times
+            // +-1, and the sign only depends on the symbol i - m: 16 + MT - 1 sign registers, then ONE FFMA per tap and output
+            // (the product by +-1 is exact, so this equals adding the sign-flipped tap, as the edge path does).
+            float sg[TX_GROUP + MT - 1];                                   // sg[d + MT - 1]: symbol s_first + d
+#pragma unroll
+            for (int d = 0; d < TX_GROUP + MT - 1; d++)
+                sg[d] = __uint_as_float(0x3F800000u | ((uint32_t)(w >> (49 - MT + d)) << 31));
 #pragma unroll
             for (int m = 0; m < MT; m++) {
-                const uint32_t hb = __float_as_uint((m < M && r + m * sps < n_taps) ? amp * __ldg(taps + r + m * sps) : 0.f);
-                const uint32_t x = (uint32_t)(w >> (48 - m));              // bit i = symbol s_first + i - m
+                const float hm = (m < M && r + m * sps < n_taps) ? amp * __ldg(taps + r + m * sps) : 0.f;
 #pragma unroll
-                for (int i = 0; i < TX_GROUP; i++)
-                    acc[i] += __uint_as_float(hb ^ ((x << (31 - i)) & 0x80000000u));
+                for (int i = 0; i < TX_GROUP; i++) acc[i] = fmaf(sg[i - m + MT - 1], hm, acc[i]);
             }
         } else {
             // first symbols of a stream (zero state before the history) and the ragged end
