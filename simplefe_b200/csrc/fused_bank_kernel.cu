@@ -26,6 +26,7 @@
 #include <cstdlib>
 #include <map>
 #include <mutex>
+#include <tuple>
 
 #include "kernels.h"
 
@@ -561,6 +562,37 @@ int bank_max_live() { return A_MAX; }
 int bank_nc(int Tc, int spc) { return (Tc + 2 * spc - 2) / spc; }
 int bank_row_len(int Tc, int spc) { return spc * (bank_nc(Tc, spc) + 2 * PAD_CHUNKS); }
 
+// A tensor map depends only on (base, extents, pitch): streaming callers present the same few buffers call after call,
+// and an encode costs about as much as a small launch, so the descriptors are memoised (bounded, per process).
+struct MapKey {
+    const void *base;
+    long a, rows, pitch;
+    int dims;
+    bool operator<(const MapKey &o) const
+    {
+        return std::tie(base, a, rows, pitch, dims) < std::tie(o.base, o.a, o.rows, o.pitch, o.dims);
+    }
+};
+static bool cached_map(CUtensorMap *m, int dims, const void *base, long a, long rows, long pitch)
+{
+    static std::mutex mu;
+    static std::map<MapKey, CUtensorMap> cache;
+    const MapKey k{base, a, rows, pitch, dims};
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = cache.find(k);
+        if (it != cache.end()) {
+            *m = it->second;
+            return true;
+        }
+    }
+    if (!(dims == 2 ? encode_rows(m, base, a, rows, pitch) : encode_rows3(m, base, a, rows, pitch))) return false;
+    std::lock_guard<std::mutex> lk(mu);
+    if (cache.size() > 256) cache.clear();
+    cache[k] = *m;
+    return true;
+}
+
 static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
 {
     BankParams p = p_in;
@@ -581,14 +613,14 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
     CUtensorMap mc, mh, mc3, mh3;
     // tensor maps count 32-bit words: one int16 sample or two u8 samples
     const long n_words = (p.in.n * eb + 3) / 4, pitch_words = p.in.pitch * eb / 4, hist_words = (long)p.H * eb / 4;
-    if (!encode_rows(&mc, p.in.cur, n_words, p.n_streams, pitch_words) ||
-        !encode_rows3(&mc3, p.in.cur, p.in.n * eb / (BOX_SAMPLES * 4), p.n_streams, pitch_words))
+    if (!cached_map(&mc, 2, p.in.cur, n_words, p.n_streams, pitch_words) ||
+        !cached_map(&mc3, 3, p.in.cur, p.in.n * eb / (BOX_SAMPLES * 4), p.n_streams, pitch_words))
         return SFE_ERR_CUDA;
     if (p.H == 0) {                          // no history rows (time-split launches): the maps are never used
         mh = mc;
         mh3 = mc3;
-    } else if (!encode_rows(&mh, p.in.hist, hist_words, p.n_streams, hist_words) ||
-               !encode_rows3(&mh3, p.in.hist, hist_words / BOX_SAMPLES, p.n_streams, hist_words)) {
+    } else if (!cached_map(&mh, 2, p.in.hist, hist_words, p.n_streams, hist_words) ||
+               !cached_map(&mh3, 3, p.in.hist, hist_words / BOX_SAMPLES, p.n_streams, hist_words)) {
         return SFE_ERR_CUDA;
     }
     int dev = 0;
