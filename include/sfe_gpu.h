@@ -202,7 +202,8 @@ int sfe_rx_feed_callback(unsigned char *buffer, int length, void *feed);
    buffered through the chain and appends the complex64 outputs to `out` (host memory, cap in samples); waits
    up to wait_ms for the first block.  Returns the number of output samples, or a negative status. */
 long sfe_rx_feed_pump(sfe_rx_feed *f, void *out, long cap, int wait_ms);
-/* which: 0 overflows ("O"), 1 discarded odd packets, 2 bytes accepted, 3 bytes waiting in the ring */
+/* which: 0 overflows ("O"), 1 discarded odd packets, 2 bytes accepted, 3 bytes waiting in the ring,
+   4 the most output samples one block can produce (pump needs at least that much room in `out`) */
 long sfe_rx_feed_stat(sfe_rx_feed *f, int which);
 
 /* ---- sample format helpers (device wire formats) ---------------------- */

@@ -135,6 +135,7 @@ extern "C" long sfe_rx_feed_stat(sfe_rx_feed *f, int which)
         case 1: return f->discarded;
         case 2: return f->bytes_in;
         case 3: return sfe_ring_count(f->ring);
+        case 4: return f->out_cap;
         default: return SFE_ERR_ARG;
     }
 }

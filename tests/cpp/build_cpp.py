@@ -30,6 +30,12 @@ def build(verbose=False):
     subprocess.run(["g++", "-O2", "-std=c++11", "-I" + INC, os.path.join(HERE, "dropin_check.cxx"), "-o", exe] + _link_flags(BIN),
                    check=True)
     built.append(exe)
+    # GNU Radio block against stand-in gnuradio/boost headers: compile + link + run check
+    exe_gr = os.path.join(BIN, "gr_block_check")
+    subprocess.run(["g++", "-O2", "-std=c++11", "-pthread", "-I" + os.path.join(HERE, "stubs"), "-I" + os.path.join(ROOT, "include"),
+                    os.path.join(HERE, "gr_block_check.cxx"), os.path.join(ROOT, "simplefe_b200", "gr", "gpu_source_c_impl.cc"),
+                    "-o", exe_gr] + _link_flags(BIN), check=True)
+    built.append(exe_gr)
     if os.path.isdir(os.path.join(REF, "libdsp")):
         os.makedirs(REFOUT, exist_ok=True)
         exe2 = os.path.join(REFOUT, "test_blkconv_gpu")
