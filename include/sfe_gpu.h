@@ -140,8 +140,9 @@ int sfe_chain_process_host(sfe_chain *c, const void *h_in, long n_in, long in_pi
                            long out_pitch, long *n_out);
 /* describe the kernels the last process call used, e.g. "toeplitz_i8+polyphase_generic" */
 const char *sfe_chain_plan(sfe_chain *c);
-/* Per-kernel timing for roofline reports: when enabled, sfe_chain_process_dev brackets the main
-   kernel of every op with CUDA events on the caller's stream (cost: two event records per op). */
+/* Per-kernel timing for roofline reports: sfe_chain_process_dev brackets the main kernel of every op with
+   CUDA events on the caller's stream in every `on`-th call (1 = every call, 0 = off).  A bracketed call costs
+   two event records per op and keeps the state-carry kernel from overlapping the main kernel's tail. */
 int sfe_chain_n_ops(sfe_chain *c);
 const char *sfe_chain_op_name(sfe_chain *c, int op);
 int sfe_chain_profile_enable(sfe_chain *c, int on);

@@ -85,7 +85,8 @@ class Chain:
     def plan(self) -> str:
         return self._l.sfe_chain_plan(self._h).decode()
 
-    def profile(self, on: bool = True):
+    def profile(self, on=True):
+        """bracket the main kernels of every `on`-th process call with CUDA events (True/1 = every call, 0 = off)"""
         check(self._l.sfe_chain_profile_enable(self._h, int(on)), "sfe_chain_profile_enable")
 
     def profile_read(self):

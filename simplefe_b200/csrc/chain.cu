@@ -94,7 +94,9 @@ struct sfe_chain {
     int cur = 0;                   // which history buffer holds the live state
     Workspace ws[2];
     std::string plan;
-    bool profile = false;
+    bool profile = false;          // bracket the main kernels of THIS call with events
+    int profile_every = 0;         // 0 = off, n = every n-th process call
+    long profile_calls = 0;
 };
 
 namespace {
@@ -188,6 +190,7 @@ bool ensure(void **p, size_t *have, size_t need)
 // host part of a call: advance every op's schedule for n_in new samples per stream
 void plan_call(sfe_chain *c, long n_in)
 {
+    c->profile = c->profile_every > 0 && (c->profile_calls++ % c->profile_every) == 0;
     long n = n_in;
     for (Op &op : c->ops) {
         op.n_in = n;
@@ -361,7 +364,7 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             if (!SFE_CUDA(cudaEventRecord(e1, st))) return SFE_ERR_CUDA;
             op.ev.emplace_back(e0, e1);
         }
-        rc = launch_save_tail(hist_new, hist_old, src, src_pitch, op.n_in, op.H, eb, ns, st);
+        rc = launch_save_tail(hist_new, hist_old, src, src_pitch, op.n_in, op.H, eb, ns, st, op.kind == OP_BANK && !e0);
         if (rc != SFE_OK) return rc;
         src = dst;
         src_pitch = dst_pitch;
@@ -637,7 +640,9 @@ extern "C" const char *sfe_chain_op_name(sfe_chain *c, int op)
 extern "C" int sfe_chain_profile_enable(sfe_chain *c, int on)
 {
     if (!c) return SFE_ERR_ARG;
-    c->profile = on != 0;
+    c->profile_every = on > 0 ? on : 0;
+    c->profile_calls = 0;
+    c->profile = false;
     return SFE_OK;
 }
 extern "C" int sfe_chain_profile_read(sfe_chain *c, int op, float *mean_ms, int *n_samples)

@@ -277,6 +277,10 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[WARPS * NST];
 
+    // The state carry that follows in the stream (save_tail) reads the same inputs and writes a buffer this kernel never
+    // touches: once the last wave of CTAs is resident it may start, filling the SMs this kernel's tail leaves idle.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *sbase = smem + ((1024u - (smem_u32(smem) & 1023u)) & 1023u);   // SWIZZLE_128B boxes: 1024 B alignment
     float *table = reinterpret_cast<float *>(sbase + (size_t)WARPS * NST * SLOT_BYTES);

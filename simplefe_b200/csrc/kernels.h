@@ -120,8 +120,10 @@ int launch_bpsk_tx(const uint32_t *bits, long pitch_words, const uint64_t *hist_
 
 // ---- small utilities (util_kernels.cu) -----------------------------------------------------------
 // hist_new[s][0..H) <- last H samples of (hist_old ++ cur[0..n)) for every stream row; elem = bytes per sample
+// overlap_prev: the kernel launched just before on `st` neither writes `cur`/`hist_old` nor touches `hist_new`, so this one
+// may start as soon as that kernel allows it (programmatic dependent launch) instead of after its last CTA
 int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long pitch, long n, int H, int elem, int n_streams,
-                     cudaStream_t st);
+                     cudaStream_t st, bool overlap_prev = false);
 int launch_pack_dac10(const float *in, long n, uint8_t *out, cudaStream_t st);
 
 }  // namespace sfe

@@ -1,6 +1,8 @@
 // util_kernels.cu -- state carry and wire-format helpers.
 #include "kernels.h"
 
+#include <cstdlib>
+
 namespace sfe {
 
 namespace {
@@ -42,15 +44,26 @@ __global__ void pack_dac10_kernel(const float *in, long n4, uint8_t *out)
 }  // namespace
 
 int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long pitch, long n, int H, int elem,
-                     int n_streams, cudaStream_t st)
+                     int n_streams, cudaStream_t st, bool overlap_prev)
 {
     if (H <= 0 || n_streams <= 0) return SFE_OK;
+    static const bool no_pdl = getenv("SFE_NO_PDL") != nullptr;
     const int u = elem / 2;
     const int H_u = H * u;
     dim3 grid((unsigned)((H_u + 255) / 256), (unsigned)n_streams);
     if (grid.x > 64) grid.x = 64;
-    save_tail_kernel<<<grid, 256, 0, st>>>(static_cast<uint16_t *>(hist_new), static_cast<const uint16_t *>(hist_old),
-                                           static_cast<const uint16_t *>(cur), pitch * u, n * u, H_u, n_streams);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = overlap_prev && !no_pdl ? 1 : 0;
+    if (!SFE_CUDA(cudaLaunchKernelEx(&cfg, save_tail_kernel, static_cast<uint16_t *>(hist_new), static_cast<const uint16_t *>(hist_old),
+                                     static_cast<const uint16_t *>(cur), pitch * u, n * u, H_u, n_streams)))
+        return SFE_ERR_CUDA;
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }
