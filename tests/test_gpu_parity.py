@@ -191,6 +191,28 @@ def test_chain_linearity_full_size_stream(gpu_lib):
     assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
 
 
+@pytest.mark.parametrize("name,S,fmt,flags", [("cfg1", 1, None, 0), ("cfg2", 1, None, 0), ("cfg3", 1, None, 0), ("cfg4", 1, None, 0),
+                                              ("cfg5", 48, None, 0), ("cfg5", 40, F.IN_U8, 0), ("cfg5", 40, None, 8), ("cfg2", 40, None, 0),
+                                              ("cfg1", 3, F.IN_I16, 0)])
+def test_baseline_configs_at_full_size_vs_oracle(gpu_lib, oracle_lib, name, S, fmt, flags):
+    """every BASELINE config at the length it is worded on (2^20 / 10^7 samples per stream; cfg 5 on 48 of its 1024
+    streams -- a ragged last group of 32 -- the oracle needs ~0.1 s per stream), fed in one call, against the
+    reference classes: same output counts, errors within north_star's tolerances"""
+    from oracle import oracle as O
+    cfg = dict(F.CONFIGS[name], S=S)
+    if fmt is not None:          # the device's u8 wire format / int16 rows into the FFT convolver
+        cfg["in_fmt"] = fmt
+    if name == "cfg2" and S > 1:
+        cfg["N"] = 1 << 20       # the many-streams flavour of cfg 2 (tcgen05 Toeplitz plan) as bench_stages.py times it
+    iq = F.make_input(cfg)
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=8)
+    ch = _chain(cfg, flags)      # flags 8 = NO_BANK: fused blkconv*decimate on the tensor cores + generic resampler
+    got = ch.process(iq)
+    assert got.shape == ref.shape, (ch.plan, got.shape, ref.shape)
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
+
+
 def test_chain_dev_pointers_and_streams(gpu_lib, oracle_lib):
     """device-resident entry point on a caller-provided CUDA stream (torch only supplies memory and the stream)"""
     import torch
