@@ -539,10 +539,6 @@ BankKernel bank_pick(const BankVariant &v, int live, int fmt)
             case 811: return bank_pick_live<8, 2, 11>(live);
             case 812: return bank_pick_live<8, 2, 12>(live);
             case 1012: return bank_pick_live<10, 2, 12>(live);
-            case 1210: return bank_pick_live<12, 2, 10>(live);
-            case 1212: return bank_pick_live<12, 2, 12>(live);
-            case 1610: return bank_pick_live<16, 2, 10>(live);
-            case 1612: return bank_pick_live<16, 2, 12>(live);
             default: return nullptr;
         }
     }

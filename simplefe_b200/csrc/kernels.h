@@ -42,6 +42,7 @@ struct PolyParams {
     float rate;           // the stage's rate (input samples per output): sizes the tile when the schedule is a table
     // filled by launch_poly_generic
     int kt, jp, tap_bytes, span_cap;
+    int cw_bytes, grp_rows;   // K2s: bytes of combined taps per warp; rows of the grouped flavour's tap table (0 = one output at a time)
 };
 int launch_poly_generic(const PolyParams &p, cudaStream_t st);
 

@@ -10,6 +10,8 @@
 #include <algorithm>
 #include <cstdlib>
 
+#include <cmath>
+
 #include "kernels.h"
 
 namespace sfe {
@@ -428,6 +430,9 @@ template <int FMT> DecimKernel decim_pick(int D, int QLP)
 // ---------------------------------------------------------------------------------------------
 constexpr int LS_WARPS = 4, LS_NT = 32 * LS_WARPS, LS_PITCH = 33;
 constexpr int LS_KPW = 16, LS_KT = LS_WARPS * LS_KPW;   // outputs per warp and per CTA, at most
+constexpr int LS_GUARD = 3;                              // zero rows in front of the staged span
+constexpr int LS_G = 4;                                  // outputs computed together in the grouped flavour
+static_assert(LS_G == 4 && LS_KPW % LS_G == 0, "the grouped loop is written for runs of four");
 
 template <int FMT> __device__ __forceinline__ float2 ls_cvt(typename DRaw<FMT>::type w);
 template <> __device__ __forceinline__ float2 ls_cvt<SFE_IN_I16>(uint32_t w) { return cvt_i16(w); }
@@ -439,15 +444,17 @@ template <> __device__ __forceinline__ float2 ls_cvt<SFE_IN_F32>(f32x2 w)
     return r;
 }
 
-template <int FMT>
+template <int FMT, bool GRP>
 __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
 {
     typedef typename DRaw<FMT>::type RT;
     extern __shared__ __align__(16) unsigned char ls_sm[];
     const int J = p.jp;                                                    // taps per phase (padded to odd)
     float *tp = reinterpret_cast<float *>(ls_sm);                          // [up][J] phase major
-    f32x2 *cb = reinterpret_cast<f32x2 *>(ls_sm + p.tap_bytes);            // [LS_WARPS][J + 1] combined taps (c, c)
-    float2 *xs = reinterpret_cast<float2 *>(cb + LS_WARPS * (J + 1));      // [span][LS_PITCH]; reused for the outputs
+    const int JC = (J + 1 + 3) & ~3;                                       // combined taps per output, zero padded to fours
+    f32x2 *cb = reinterpret_cast<f32x2 *>(ls_sm + p.tap_bytes);            // [LS_WARPS][JC] combined taps (c, c)
+    // [LS_GUARD + span][LS_PITCH]; reused for the outputs.  The guard rows in front are zero: the padding taps read them.
+    float2 *xs = reinterpret_cast<float2 *>(ls_sm + p.tap_bytes + LS_WARPS * p.cw_bytes) + LS_GUARD * LS_PITCH;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     const long k0 = (long)blockIdx.x * p.kt;
@@ -477,6 +484,15 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
         const int ph = i / J, j = i - ph * J, m = ph + j * p.up;
         tp[i] = m < p.n_taps ? __ldg(p.taps + m) : 0.f;
     }
+    for (int i = threadIdx.x; i < LS_GUARD * LS_PITCH; i += LS_NT) xs[i - LS_GUARD * LS_PITCH] = make_float2(0.f, 0.f);
+    // the warp's schedule entries, one per lane, fetched now so that their latency hides behind the staging loads
+    // register slot q of warp w holds output k0 + kl(q): outputs w, w + 4, ... one at a time, or (GRP) runs of LS_G
+    // consecutive outputs that are computed together
+    auto kl_of = [&](int q) { return GRP ? LS_G * (warp + LS_WARPS * (q / LS_G)) + (q % LS_G) : warp + LS_WARPS * q; };
+    long pos_l = 0;
+    float mu_l = 0.f;
+    if (lane < LS_KPW && k0 + kl_of(lane) <= k1) poly_sched(p, k0 + kl_of(lane), pos_l, mu_l);
+    const int pos_li = (int)pos_l;                                         // positions of one call fit 32 bits (SchedEntry)
     // ---- stage the span transposed: warp w takes rows w, w + 4, ...; lanes run along the samples ----
     const bool interior = n_lo >= 0 && n_hi < p.in.n;
     if (interior) {
@@ -487,6 +503,18 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
             const int s = min(s0 + warp + LS_WARPS * rr, p.n_streams - 1);   // rows past the end repeat the last stream (never stored)
             src[rr] = reinterpret_cast<const RT *>(p.in.cur) + (long)s * p.in.pitch + n_lo;
         }
+        if (FMT == SFE_IN_F32) {
+            // complex64 rows need no conversion: 8-byte asynchronous copies straight into the transposed tile, the whole
+            // span of the CTA in flight at once instead of 16 loads per lane and round
+            for (int i0 = lane; i0 < span; i0 += 32) {
+#pragma unroll
+                for (int rr = 0; rr < 32 / LS_WARPS; rr++) {
+                    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(xs + i0 * LS_PITCH + warp + LS_WARPS * rr);
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src[rr] + i0) : "memory");
+                }
+            }
+            asm volatile("cp.async.commit_group;\n cp.async.wait_group 0;" ::: "memory");
+        } else
         for (int i0 = lane; i0 < span; i0 += 64) {
             RT raw[2][32 / LS_WARPS];
 #pragma unroll
@@ -509,52 +537,108 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
     __syncthreads();
     // ---- compute: warp w takes outputs k0 + w, k0 + w + 4, ...; every lane its own stream ----
     f32x2 res[LS_KPW];
-    f32x2 *cw = cb + warp * (J + 1);
+    if (GRP) {
+        // LS_G consecutive outputs share most of their samples (the launcher picks this flavour when the windows overlap
+        // by half or more): their combined taps are laid out on one sample axis, m = newest sample of the run - sample,
+        // as rows of LS_G (c, c) pairs, zero outside each output's window.  Per sample one LDS.64 of the lane's own
+        // stream and two broadcast LDS.128 feed LS_G FFMA2 -- 4 shared-memory wavefronts instead of 10.
+        ulonglong2 *ct = reinterpret_cast<ulonglong2 *>(ls_sm + p.tap_bytes + warp * p.cw_bytes);   // [rows][LS_G / 2]
+        const int g = lane & (LS_G - 1);
 #pragma unroll
-    for (int q = 0; q < LS_KPW; q++) {
-        res[q] = 0ull;
-        const long k = k0 + warp + LS_WARPS * q;
-        if (k > k1) continue;                                              // warp uniform
-        long pos;
-        float mu;
-        poly_sched(p, k, pos, mu);
-        const long n0 = floordiv(pos, p.up);
-        const int ph0 = (int)(pos - n0 * p.up);
-        int ph1 = ph0 + 1, d = 0;
-        if (ph1 == p.up) { ph1 = 0; d = 1; }
-        const float *t0 = tp + ph0 * J, *t1 = tp + ph1 * J;
-        const float w0 = 1.0f - mu;
-        __syncwarp();                                                      // the previous output's readers are done
-        for (int i = lane; i < J + d; i += 32) {
-            const float a = i < J ? t1[i] : 0.f, b = (i - d >= 0 && i - d < J) ? t0[i - d] : 0.f;
-            const float c = mu != 0.f ? fmaf(mu, a, w0 * b) : b;           // mu == 0: exactly the taps of s(pos)
-            cw[i] = d_pack2(c, c);
+        for (int qq = 0; qq < LS_KPW / LS_G; qq++) {
+#pragma unroll
+            for (int u = 0; u < LS_G; u++) res[qq * LS_G + u] = 0ull;
+            const long kg = k0 + kl_of(qq * LS_G);
+            if (kg > k1) continue;                                         // warp uniform
+            // every lane derives the window of output g = lane % LS_G of the run
+            const int pos = __shfl_sync(0xffffffffu, pos_li, qq * LS_G + g);
+            const float mu = __shfl_sync(0xffffffffu, mu_l, qq * LS_G + g);
+            const bool valid = kg + g <= k1;
+            const int n0 = (int)floordiv(pos, p.up);
+            const int ph0 = pos - n0 * p.up;
+            int ph1 = ph0 + 1, d = 0;
+            if (ph1 == p.up) { ph1 = 0; d = 1; }
+            const int row = (int)(n0 + d - n_lo);                          // row of x[n_top] in the staged span
+            const int row_hi = __reduce_max_sync(0xffffffffu, valid ? row : 0);
+            const int off = row_hi - row;
+            int M = __reduce_max_sync(0xffffffffu, valid ? off + J + d : 0);
+            M = min((M + 1) & ~1, p.grp_rows);                             // two samples per round; the launcher sized the table for 3 steps + J
+            const float *t0 = tp + ph0 * J, *t1 = tp + ph1 * J;
+            const float w0 = 1.0f - mu;
+            __syncwarp();                                                  // the previous run's readers are done
+            f32x2 *cf = reinterpret_cast<f32x2 *>(ct);
+            for (int m = lane / LS_G; m < M; m += 32 / LS_G) {
+                const int i = m - off;
+                const float a = (valid && i >= 0 && i < J) ? t1[i] : 0.f;
+                const float b = (valid && i - d >= 0 && i - d < J) ? t0[i - d] : 0.f;
+                const float c = mu != 0.f ? fmaf(mu, a, w0 * b) : b;
+                cf[m * LS_G + g] = d_pack2(c, c);
+            }
+            __syncwarp();
+            const f32x2 *xq = reinterpret_cast<const f32x2 *>(xs + row_hi * LS_PITCH + lane);
+            const ulonglong2 *cq = ct;
+            f32x2 a0 = 0ull, a1 = 0ull, a2 = 0ull, a3 = 0ull;
+            for (int m = 0; m < M; m += 2, xq -= 2 * LS_PITCH, cq += LS_G) {
+                const f32x2 x0 = xq[0], x1 = xq[-LS_PITCH];
+                const ulonglong2 c01 = cq[0], c23 = cq[1], e01 = cq[2], e23 = cq[3];
+                a0 = d_ffma2(c01.x, x0, a0);
+                a1 = d_ffma2(c01.y, x0, a1);
+                a2 = d_ffma2(c23.x, x0, a2);
+                a3 = d_ffma2(c23.y, x0, a3);
+                a0 = d_ffma2(e01.x, x1, a0);
+                a1 = d_ffma2(e01.y, x1, a1);
+                a2 = d_ffma2(e23.x, x1, a2);
+                a3 = d_ffma2(e23.y, x1, a3);
+            }
+            res[qq * LS_G + 0] = a0;
+            res[qq * LS_G + 1] = a1;
+            res[qq * LS_G + 2] = a2;
+            res[qq * LS_G + 3] = a3;
         }
-        __syncwarp();
-        const float2 *xp = xs + (int)(n0 + d - n_lo) * LS_PITCH + lane;    // x[n_top] of this lane's stream
-        f32x2 acc = 0ull, acc2 = 0ull;
-        const int nt = J + d;
-        int i = 0;
-        for (; i + 3 < nt; i += 4) {                                       // four taps per round, all loads first
-            const f32x2 c0 = cw[i], c1 = cw[i + 1], c2 = cw[i + 2], c3 = cw[i + 3];
-            const f32x2 x0 = *reinterpret_cast<const f32x2 *>(xp - i * LS_PITCH);
-            const f32x2 x1 = *reinterpret_cast<const f32x2 *>(xp - (i + 1) * LS_PITCH);
-            const f32x2 x2 = *reinterpret_cast<const f32x2 *>(xp - (i + 2) * LS_PITCH);
-            const f32x2 x3 = *reinterpret_cast<const f32x2 *>(xp - (i + 3) * LS_PITCH);
-            acc = d_ffma2(c0, x0, acc);
-            acc2 = d_ffma2(c1, x1, acc2);
-            acc = d_ffma2(c2, x2, acc);
-            acc2 = d_ffma2(c3, x3, acc2);
+    } else {
+        f32x2 *cw = cb + warp * JC;
+    #pragma unroll
+        for (int q = 0; q < LS_KPW; q++) {
+            res[q] = 0ull;
+            const long k = k0 + warp + LS_WARPS * q;
+            if (k > k1) continue;                                              // warp uniform
+            const long pos = __shfl_sync(0xffffffffu, pos_li, q);
+            const float mu = __shfl_sync(0xffffffffu, mu_l, q);
+            const long n0 = floordiv(pos, p.up);
+            const int ph0 = (int)(pos - n0 * p.up);
+            int ph1 = ph0 + 1, d = 0;
+            if (ph1 == p.up) { ph1 = 0; d = 1; }
+            const float *t0 = tp + ph0 * J, *t1 = tp + ph1 * J;
+            const float w0 = 1.0f - mu;
+            __syncwarp();                                                      // the previous output's readers are done
+            for (int i = lane; i < JC; i += 32) {
+                const float a = i < J ? t1[i] : 0.f, b = (i - d >= 0 && i - d < J) ? t0[i - d] : 0.f;
+                const float c = mu != 0.f ? fmaf(mu, a, w0 * b) : b;           // mu == 0: exactly the taps of s(pos)
+                cw[i] = d_pack2(c, c);                                         // i >= J + d: zero padding
+            }
+            __syncwarp();
+            // x[n_top] of this lane's stream; four taps per round: two 128-bit tap loads, four sample loads at constant
+            // offsets from one moving pointer.  The padding taps meet rows of the span or of the zero guard in front of it.
+            const f32x2 *xq = reinterpret_cast<const f32x2 *>(xs + (int)(n0 + d - n_lo) * LS_PITCH + lane);
+            const ulonglong2 *cq = reinterpret_cast<const ulonglong2 *>(cw);
+            f32x2 acc = 0ull, acc2 = 0ull;
+            for (int i = 0; i < JC; i += 4, xq -= 4 * LS_PITCH, cq += 2) {
+                const ulonglong2 c01 = cq[0], c23 = cq[1];
+                const f32x2 x0 = xq[0], x1 = xq[-LS_PITCH], x2 = xq[-2 * LS_PITCH], x3 = xq[-3 * LS_PITCH];
+                acc = d_ffma2(c01.x, x0, acc);
+                acc2 = d_ffma2(c01.y, x1, acc2);
+                acc = d_ffma2(c23.x, x2, acc);
+                acc2 = d_ffma2(c23.y, x3, acc2);
+            }
+            res[q] = d_fadd2(acc, acc2);
         }
-        for (; i < nt; i++) acc = d_ffma2(cw[i], *reinterpret_cast<const f32x2 *>(xp - i * LS_PITCH), acc);
-        res[q] = d_fadd2(acc, acc2);
     }
     __syncthreads();                                                       // all reads of xs are done: reuse it
     f32x2 *ob = reinterpret_cast<f32x2 *>(xs);                             // [32 streams][kt + 1]
     const int opitch = p.kt + 1;
 #pragma unroll
     for (int q = 0; q < LS_KPW; q++) {
-        const int kl = warp + LS_WARPS * q;
+        const int kl = kl_of(q);
         if (k0 + kl <= k1) ob[lane * opitch + kl] = res[q];
     }
     __syncthreads();
@@ -593,8 +677,16 @@ int launch_poly_generic(const PolyParams &p_in, cudaStream_t st)
             p.tap_bytes = (int)tap_bytes;
             p.span_cap = (int)std::min<long>(cap_s, (long)((double)kl * per_out * 1.01) + p.jp + 8);
             const size_t body = std::max<size_t>((size_t)p.span_cap * LS_PITCH * 8, (size_t)32 * (kl + 1) * 8);
-            const size_t smem_l = tap_bytes + (size_t)LS_WARPS * (p.jp + 1) * 8 + body;
-            auto kl_kern = p.in.fmt == SFE_IN_I16 ? poly_lanes_kernel<SFE_IN_I16> : p.in.fmt == SFE_IN_U8 ? poly_lanes_kernel<SFE_IN_U8> : poly_lanes_kernel<SFE_IN_F32>;
+            // runs of LS_G outputs are computed together when their windows overlap by half or more (and the table stays small)
+            static const bool no_grp = getenv("SFE_POLY_NO_GROUP") != nullptr;   // tuning hook
+            const int grp_rows = ((int)std::ceil((LS_G - 1) * (per_out + 1.0)) + p.jp + 1 + 4 + 1) & ~1;
+            const bool grp = !no_grp && (LS_G - 1) * per_out <= p.jp && grp_rows <= 128 && kl % (LS_WARPS * LS_G) == 0;
+            p.grp_rows = grp ? grp_rows : 0;
+            p.cw_bytes = grp ? grp_rows * LS_G * 8 : ((p.jp + 1 + 3) & ~3) * 8;
+            const size_t smem_l = tap_bytes + (size_t)LS_WARPS * p.cw_bytes + (size_t)LS_GUARD * LS_PITCH * 8 + body;
+            typedef void (*LanesKernel)(const PolyParams);
+            LanesKernel kl_kern = grp ? (p.in.fmt == SFE_IN_I16 ? poly_lanes_kernel<SFE_IN_I16, true> : p.in.fmt == SFE_IN_U8 ? poly_lanes_kernel<SFE_IN_U8, true> : poly_lanes_kernel<SFE_IN_F32, true>)
+                                      : (p.in.fmt == SFE_IN_I16 ? poly_lanes_kernel<SFE_IN_I16, false> : p.in.fmt == SFE_IN_U8 ? poly_lanes_kernel<SFE_IN_U8, false> : poly_lanes_kernel<SFE_IN_F32, false>);
             if (smem_l > 48 * 1024 && !SFE_CUDA(cudaFuncSetAttribute(kl_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l)))
                 return SFE_ERR_CUDA;
             dim3 grid((unsigned)((p.n_out + kl - 1) / kl), (unsigned)((p.n_streams + 31) / 32));
