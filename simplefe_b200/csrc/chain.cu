@@ -497,7 +497,7 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
             // windows open and close on box boundaries: at most one may open per box, and a box is overlapped by
             // the windows whose first chunk lies in a range of NC + 7 chunks
             const long live = spacing >= 2 * box ? (NC + 6) / (spacing / spc) + 1 : 1 << 30;
-            if (live <= bank_max_live() && bank_smem_bytes(op.n_rows, op.row_len) <= 227 * 1024) {
+            if (live <= bank_max_live() && bank_smem_bytes(op.n_rows, op.row_len, op.in_fmt) <= 227 * 1024) {
                 op.n_live = (int)live;
                 op.H = (spc * NC + 2 * op.D + spc + box - 1) / box * box;
                 op.name = std::string("bank_fused(") + (has_bc ? "blkconv*" : "") + (has_b ? "decim*" : "") + "polyphase)/L" +

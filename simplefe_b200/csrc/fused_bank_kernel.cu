@@ -269,11 +269,12 @@ __device__ __forceinline__ void split_pos(const BankParams &p, long k, long &M, 
     if (ph < 0) { ph += p.L; M -= 1; }                    // floor division: pos = -1 is a held-over output
 }
 
-template <int WARPS, int NST, int CONV, int NLIVE>
+template <int WARPS, int NST, int CONV, int NLIVE, int SB = SLOT_BOXES>   // SB: boxes per ring slot (2: one 3-D box, 1: one 2-D box)
 __global__ void __launch_bounds__(WARPS * 32, 1)
 fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_constant__ CUtensorMap map_hist,
                   const __grid_constant__ CUtensorMap map_cur3, const __grid_constant__ CUtensorMap map_hist3, const BankParams p)
 {
+    constexpr int SLOT_B = SB * BOX_BYTES;                           // bytes per ring slot
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[WARPS * NST];
 
@@ -283,8 +284,8 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *sbase = smem + ((1024u - (smem_u32(smem) & 1023u)) & 1023u);   // SWIZZLE_128B boxes: 1024 B alignment
-    float *table = reinterpret_cast<float *>(sbase + (size_t)WARPS * NST * SLOT_BYTES);
-    const uint32_t ring_a = smem_u32(sbase) + (uint32_t)warp * NST * SLOT_BYTES;
+    float *table = reinterpret_cast<float *>(sbase + (size_t)WARPS * NST * SLOT_B);
+    const uint32_t ring_a = smem_u32(sbase) + (uint32_t)warp * NST * SLOT_B;
     const uint32_t table_a = smem_u32(table);
 
     // ---- one-time: bank table -> shared memory, barriers ------------------------------------------------
@@ -325,8 +326,8 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     const int q_begin = first.E - NC + 1, q_end = last.E;          // chunks this item reads (inclusive)
     const int box0 = q_begin >> 3;                                 // 8 chunks per box
     const int n_boxes = (q_end >> 3) - box0 + 1;
-    const int slot0 = box0 >> 1;                                   // slots pair boxes (2a, 2a+1) of the absolute box grid
-    const int n_slots = (q_end >> 4) - slot0 + 1;
+    const int slot0 = box0 / SB;                                   // SB = 2: slots pair boxes (2a, 2a+1) of the absolute box grid
+    const int n_slots = (q_end >> 3) / SB - slot0 + 1;
     const int hist_boxes = p.H / (8 * SPC);                        // a box = 128 bytes = 8 chunks per row
     const int full_tb = (int)(p.in.n / (8 * SPC));                 // whole 128-byte time blocks of the current rows
     const uint32_t bar0 = smem_u32(&bars[warp * NST]);
@@ -337,19 +338,19 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     // out-of-range samples the TMA zero-fills.
     auto slot_3d = [&](int a) -> bool {
         const int b0 = 2 * a, b1 = 2 * a + 1;
-        return b1 < hist_boxes || (b0 >= hist_boxes && b1 - hist_boxes < full_tb);
+        return SB == 2 && (b1 < hist_boxes || (b0 >= hist_boxes && b1 - hist_boxes < full_tb));
     };
     auto issue = [&](int a, int rs) {                              // lane 0 only; a = absolute slot, rs = ring slot
         const uint32_t bar = bar0 + 8 * rs;
-        mbar_expect_tx(bar, SLOT_BYTES);
-        const uint32_t dst = ring_a + rs * SLOT_BYTES;
-        const int b0 = 2 * a;                                      // box b holds samples [32 b - H, 32 b - H + 32)
+        mbar_expect_tx(bar, SLOT_B);
+        const uint32_t dst = ring_a + rs * SLOT_B;
+        const int b0 = SB * a;                                     // box b holds samples [32 b - H, 32 b - H + 32)
         if (slot_3d(a)) {
             if (b0 < hist_boxes) tma_box3(dst, &map_hist3, b0, g * BOX_ROWS, bar);
             else tma_box3(dst, &map_cur3, b0 - hist_boxes, g * BOX_ROWS, bar);
         } else {
 #pragma unroll
-            for (int t = 0; t < SLOT_BOXES; t++) {
+            for (int t = 0; t < SB; t++) {
                 const int box = b0 + t;
                 if (box < hist_boxes) tma_box(dst + t * BOX_BYTES, &map_hist, box * BOX_SAMPLES, g * BOX_ROWS, bar);
                 else tma_box(dst + t * BOX_BYTES, &map_cur, (box - hist_boxes) * BOX_SAMPLES, g * BOX_ROWS, bar);
@@ -385,7 +386,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     int slot = 0;
     uint32_t phase = 0;
     for (int bi = 0; bi < n_boxes; bi++) {
-        const int B = box0 + bi, a = B >> 1, tb = B & 1;
+        const int B = box0 + bi, a = B / SB, tb = B % SB;
         if (bi == 0 || tb == 0) mbar_wait(bar0 + 8 * slot, phase);   // first box of a slot
         if (B == open_box) {                                         // a window opens in this box (at most one)
             const int S = nxt.E - NC + 1;                            // its first chunk
@@ -411,7 +412,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
         }
         // this lane's 128-byte line of the box: 3-D slot: line 2 lane + tb; 2-D boxes: box tb, line lane
         const uint32_t line = slot_3d(a) ? (uint32_t)(2 * lane + tb) : (uint32_t)(tb * BOX_ROWS + lane);
-        const uint32_t ax = ring_a + slot * SLOT_BYTES + line * 128u + ((line & 7u) << 4);
+        const uint32_t ax = ring_a + slot * SLOT_B + line * 128u + ((line & 7u) << 4);
         run_box<NLIVE, CONV>(ax, accI, accQ, tp);
         if (B == Eb[0]) {                                            // the oldest window is complete
             const float2 yi = unpack2(accI[0]), yq = unpack2(accQ[0]);
@@ -430,7 +431,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
 #pragma unroll
         for (int j = 0; j < NLIVE; j++)
             if (j >= nact) tp[j] = table_a;                          // idle slots stay on the zero pad
-        if (tb == 1 || bi == n_boxes - 1) {                          // slot consumed: refill it, move on
+        if (tb == SB - 1 || bi == n_boxes - 1) {                          // slot consumed: refill it, move on
             __syncwarp();
             if (lane == 0 && (a - slot0) + NST < n_slots) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // our reads before the next TMA write
@@ -502,31 +503,42 @@ bool encode_rows3(CUtensorMap *m, const void *base, long n_blocks, long n_rows, 
 
 // ---- launch variants: warps per CTA, ring slots per warp, conversion flavour ----------------------------------
 struct BankVariant {
-    int warps, nst, conv, conv8;   // conv: int16 flavour (0-3), conv8: u8 flavour (10-12)
+    int warps, nst, conv, sb;      // conv: int16 flavour (0-3) or u8 flavour (10-12); sb: boxes per ring slot
 };
 typedef void (*BankKernel)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const BankParams);
 
-BankVariant bank_variant()
+// int16 rows: 8 warps x 2 slots of one 3-D box (256 contiguous bytes per row keep HBM at full rate; the kernel is HBM bound).
+// u8 rows carry twice the samples per byte, so the kernel is bound by its two warps per scheduler instead: 16 warps with
+// one-box slots (the same 128 KB of ring) give the schedulers four.
+BankVariant bank_variant(int fmt)
 {
-    static BankVariant v = [] {
-        BankVariant d{8, 2, 2, 12};
-        if (const char *e = getenv("SFE_BANK_VARIANT")) {   // tuning hook: "warps,slots,conv[,conv8]"
-            int w = 0, n = 0, c = 0, c8 = 12;
-            if (sscanf(e, "%d,%d,%d,%d", &w, &n, &c, &c8) >= 3) d = BankVariant{w, n, c, c8};
+    static const BankVariant v16 = [] {
+        BankVariant d{8, 2, 2, 2};
+        if (const char *e = getenv("SFE_BANK_VARIANT")) {   // tuning hook: "warps,slots,conv"
+            int w = 0, n = 0, c = 0;
+            if (sscanf(e, "%d,%d,%d", &w, &n, &c) >= 3) d = BankVariant{w, n, c, 2};
         }
         return d;
     }();
-    return v;
+    static const BankVariant v8 = [] {
+        BankVariant d{16, 2, 12, 1};
+        if (const char *e = getenv("SFE_BANK_VARIANT_U8")) {   // tuning hook: "warps,conv,boxes per slot"
+            int w = 0, c = 0, b = 0;
+            if (sscanf(e, "%d,%d,%d", &w, &c, &b) >= 3) d = BankVariant{w, 2, c, b};
+        }
+        return d;
+    }();
+    return fmt == SFE_IN_U8 ? v8 : v16;
 }
 
-template <int W, int N, int C>
+template <int W, int N, int C, int SB = SLOT_BOXES>
 BankKernel bank_pick_live(int live)
 {
     switch (live) {
-        case 1: return fused_bank_kernel<W, N, C, 1>;
-        case 2: return fused_bank_kernel<W, N, C, 2>;
-        case 3: return fused_bank_kernel<W, N, C, 3>;
-        case 4: return fused_bank_kernel<W, N, C, 4>;
+        case 1: return fused_bank_kernel<W, N, C, 1, SB>;
+        case 2: return fused_bank_kernel<W, N, C, 2, SB>;
+        case 3: return fused_bank_kernel<W, N, C, 3, SB>;
+        case 4: return fused_bank_kernel<W, N, C, 4, SB>;
         default: return nullptr;
     }
 }
@@ -534,14 +546,17 @@ BankKernel bank_pick_live(int live)
 BankKernel bank_pick(const BankVariant &v, int live, int fmt)
 {
     if (fmt == SFE_IN_U8) {
-        switch (v.warps * 100 + v.conv8) {
-            case 810: return bank_pick_live<8, 2, 10>(live);
-            case 811: return bank_pick_live<8, 2, 11>(live);
-            case 812: return bank_pick_live<8, 2, 12>(live);
-            case 1012: return bank_pick_live<10, 2, 12>(live);
+        if (v.nst != 2) return nullptr;
+        switch (v.warps * 1000 + v.conv * 10 + v.sb) {
+            case 8102: return bank_pick_live<8, 2, 10>(live);
+            case 8122: return bank_pick_live<8, 2, 12>(live);
+            case 12121: return bank_pick_live<12, 2, 12, 1>(live);
+            case 16101: return bank_pick_live<16, 2, 10, 1>(live);
+            case 16121: return bank_pick_live<16, 2, 12, 1>(live);
             default: return nullptr;
         }
     }
+    if (v.sb != 2) return nullptr;
     const int key = v.warps * 100 + v.nst * 10 + v.conv;
     switch (key) {
         case 820: return bank_pick_live<8, 2, 0>(live);
@@ -556,10 +571,10 @@ BankKernel bank_pick(const BankVariant &v, int live, int fmt)
 
 }  // namespace
 
-size_t bank_smem_bytes(int n_rows, int row_len)
+size_t bank_smem_bytes(int n_rows, int row_len, int fmt)
 {
-    const BankVariant v = bank_variant();
-    return (size_t)v.warps * v.nst * SLOT_BYTES + (size_t)n_rows * row_len * sizeof(float) + 1024;
+    const BankVariant v = bank_variant(fmt);
+    return (size_t)v.warps * v.nst * v.sb * BOX_BYTES + (size_t)n_rows * row_len * sizeof(float) + 1024;
 }
 
 int bank_max_live() { return A_MAX; }
@@ -608,7 +623,7 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
         set_error("fused bank: input rows must be int16 or u8 IQ, 16-byte aligned with a pitch that is a multiple of 16 bytes");
         return SFE_ERR_ARG;
     }
-    const BankVariant v = bank_variant();
+    const BankVariant v = bank_variant(p.in.fmt);
     BankKernel kern = bank_pick(v, p.n_live, p.in.fmt);
     if (!kern) {
         set_error("fused bank: SFE_BANK_VARIANT names a variant that is not compiled in (or n_live is out of range)");
@@ -653,7 +668,7 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
     if (n_seg < 1) n_seg = 1;
     p.n_seg = (int)n_seg;
     const long items = (long)p.n_groups * p.n_seg;
-    const size_t smem = bank_smem_bytes(p.n_rows, p.row_len);
+    const size_t smem = bank_smem_bytes(p.n_rows, p.row_len, p.in.fmt);
     {
         std::lock_guard<std::mutex> lk(cache_mutex);
         size_t &have = smem_set[{dev, reinterpret_cast<const void *>(kern)}];

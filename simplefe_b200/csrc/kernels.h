@@ -109,7 +109,7 @@ int bank_nc(int Tc, int spc);         // 16-byte chunks (spc samples each) of ta
 int bank_row_len(int Tc, int spc);    // floats per table row, zero pads included
 void bank_table(const std::vector<double> &g, int D, const std::vector<float> &r, int L, double scale, int e_only, int spc,
                 std::vector<float> &rows, int *row_len, int *n_rows, int *Tc);
-size_t bank_smem_bytes(int n_rows, int row_len);
+size_t bank_smem_bytes(int n_rows, int row_len, int fmt);
 int bank_max_live();
 int launch_bank(const BankParams &p, cudaStream_t st);
 
