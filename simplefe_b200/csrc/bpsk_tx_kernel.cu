@@ -9,23 +9,23 @@
 // computed here straight from the packed bits; the float waveform never leaves the chip when the caller asks
 // for DAC words.  The kernel is bound by its own output stream (12.5 bytes per symbol at sps = 10).
 //
-// Mapping: a CTA owns up to 2048 consecutive symbols of one channel (as many as keep its tile under 80 KB), a thread
-// 16 of them.  The thread derives the symbol signs of its group once, from one 64-bit window of the bit stream, as
-// +-1.0f registers, and then walks the phases r = 0 .. sps-1: the ~12 pre-scaled taps h[r + m*sps] of the phase come
-// from shared memory with 128-bit loads, every tap and output costs one FFMA, and the 16 results go to a shared-memory
-// tile in time order (group stride 16*sps + 2 words: 2-way instead of 32-way bank conflicts).  A second pass packs
-// the tile and stores 128-bit words.
+// Mapping: a warp owns 512 consecutive symbols of one channel, a thread 16 of them.  The thread derives the symbol signs of
+// its group once, from one 64-bit window of the bit stream, as +-1.0f registers, and then walks the phases
+// r = 0 .. sps-1: the ~12 pre-scaled taps h[r + m*sps] of the phase come from shared memory with 128-bit loads, every
+// tap and output costs one FFMA, and the 16 results go to the warp's own shared-memory tile in time order (group stride
+// 16*sps + 2 words: 2-way instead of 32-way bank conflicts).  The warp then packs its tile (DAC words: in place) and
+// stores 128-bit words.  Tiles are warp-private, so warps only meet at __syncwarp: while one warp stores, the others
+// compute (with CTA-wide tiles 22 % of the stall samples were the barrier between the two passes).
 #include "kernels.h"
 
 namespace sfe {
 
 namespace {
 
-constexpr int TX_SYM_MAX = 2048;   // symbols per CTA, at most
 constexpr int TX_GROUP = 16;       // symbols per thread
+constexpr int TX_WSYM = 32 * TX_GROUP;   // symbols per warp
 constexpr int TX_MAXM = 32;        // taps per phase, at most (n_taps <= 32 * sps)
-constexpr int TX_THREADS = TX_SYM_MAX / TX_GROUP;
-constexpr int TX_TILE_BYTES = 80 * 1024;
+constexpr int TX_MAXW = 4;         // warps per CTA, at most
 
 // bit k of the channel's symbol stream; k < 0 reads the history word (bit 63 = symbol -1)
 __device__ __forceinline__ uint64_t bits_window(const uint32_t *cur, uint64_t hist, long s_hi, long n_sym)
@@ -50,33 +50,33 @@ __device__ __forceinline__ uint64_t bits_window(const uint32_t *cur, uint64_t hi
 }
 
 template <int MT>     // taps per phase, rounded up to a multiple of 4 (the padding taps are zero)
-__global__ void __launch_bounds__(TX_THREADS)
-bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int n_hist, long n_sym, int sps, int sym_cta, const float *taps,
+__global__ void __launch_bounds__(32 * TX_MAXW)
+bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int n_hist, long n_sym, int sps, const float *taps,
                int n_taps, float amp, int out_dac10, void *out, long out_pitch_bytes)
 {
     extern __shared__ __align__(16) float tx_sm[];
     float *hs = tx_sm;                                     // [sps][MT] pre-scaled taps, hs[r][m] = amp * h[r + m*sps]
-    float *tile = hs + sps * MT;                           // [groups][16*sps + 2]: samples in time order per group
     const int gstride = TX_GROUP * sps + 2;
-    const int n_groups = sym_cta / TX_GROUP;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *tile = hs + sps * MT + warp * 32 * gstride;     // this warp's [32 groups][16*sps + 2]: samples in time order per group
     const int ch = blockIdx.y;
-    const long s0 = (long)blockIdx.x * sym_cta;
+    const long s0 = ((long)blockIdx.x * (blockDim.x >> 5) + warp) * TX_WSYM;   // first symbol of the warp
     const uint32_t *cur = bits + (long)ch * pitch_words;
     const uint64_t hw = hist[ch];
     const int M = (n_taps + sps - 1) / sps;                // taps per phase
 
-    for (int i = threadIdx.x; i < sps * MT; i += TX_THREADS) {
+    for (int i = threadIdx.x; i < sps * MT; i += blockDim.x) {
         const int r = i / MT, m = i - r * MT;
         hs[i] = (m < M && r + m * sps < n_taps) ? amp * __ldg(taps + r + m * sps) : 0.f;
     }
     __syncthreads();
+    if (s0 >= n_sym) return;                               // whole warp
 
-    for (int grp = threadIdx.x; grp < n_groups; grp += TX_THREADS) {
-        const long s_first = s0 + (long)grp * TX_GROUP;
-        if (s_first >= n_sym) break;
+    const long s_first = s0 + (long)lane * TX_GROUP;
+    if (s_first < n_sym) {
         // window: bit 63 = symbol s_first + 15, ..., bit 0 = symbol s_first - 48
         const uint64_t w = bits_window(cur, hw, s_first + TX_GROUP - 1, n_sym);
-        float *trow = tile + grp * gstride;
+        float *trow = tile + lane * gstride;
         if (s_first - (M - 1) >= -(long)n_hist && s_first + TX_GROUP <= n_sym) {
             // every symbol the group touches exists.  The +-A impulse (bpsk.cxx:150) times a tap is the pre-scaled tap times
             // +-1, and the sign only depends on the symbol i - m: 16 + MT - 1 sign registers shared by all phases, then ONE
@@ -106,8 +106,9 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
                         for (int i = 0; i < TX_GROUP; i++) acc[i] = fmaf(sg[i - m + MT - 1], hv[u], acc[i]);
                     }
                 }
+                float *tr = trow + r;
 #pragma unroll
-                for (int i = 0; i < TX_GROUP; i++) trow[i * sps + r] = acc[i];
+                for (int i = 0; i < TX_GROUP; i++, tr += sps) *tr = acc[i];
             }
         } else {
             // first symbols of a stream (zero state before the history) and the ragged end
@@ -131,9 +132,9 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
             }
         }
     }
-    __syncthreads();
+    __syncwarp();
 
-    // sample n of the tile (time order) sits at tile[(n / (16 sps)) * gstride + n % (16 sps)]; a quad never straddles a group
+    // sample n of the warp's tile (time order) sits at tile[(n / (16 sps)) * gstride + n % (16 sps)]; a quad never straddles a group
     const int qpg = TX_GROUP * sps / 4;                    // quads per group
     const uint32_t qmagic = 0xFFFFFFFFu / (uint32_t)qpg + 1u;   // floor(q / qpg) = umulhi(q, qmagic) for q < 2^16
     auto load_quad = [&](int qd) {
@@ -142,17 +143,17 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
         const float2 a = src[0], b = src[1];
         return make_float4(a.x, a.y, b.x, b.y);
     };
-    const long n_valid_sym = n_sym - s0 < sym_cta ? n_sym - s0 : sym_cta;
-    const long n_samp = n_valid_sym * sps;                 // valid samples of this tile
+    const int n_valid_sym = (int)(n_sym - s0 < TX_WSYM ? n_sym - s0 : TX_WSYM);
+    const int n_samp = n_valid_sym * sps;                  // valid samples of this tile
     const long samp0 = s0 * sps;
     char *row0 = static_cast<char *>(out) + (long)ch * out_pitch_bytes;
     if (out_dac10) {
         // bpsk.cxx:76-101: u = ((short)(x*511) + 512) & 0x3FF, 4 words -> 5 bytes, the four 2-bit tops first.
-        // Packed into a second shared-memory tile, then stored as 128-bit words.
-        uint8_t *packed = reinterpret_cast<uint8_t *>(tile + n_groups * gstride);
-        const long n_quads = n_samp / 4;
-        for (long qd = threadIdx.x; qd < n_quads; qd += TX_THREADS) {
-            const float4 x = load_quad((int)qd);
+        // Packed in place: quad q is read from bytes >= 16 q of the tile and written to bytes 5 q, so a round of 32 quads
+        // only overwrites what this and earlier rounds have read.  Then stored as 128-bit words.
+        uint8_t *packed = reinterpret_cast<uint8_t *>(tile);
+        const int n_quads = n_samp / 4;
+        auto pack_quad = [](const float4 &x, uint32_t (&b)[5]) {
             const float v[4] = {x.x, x.y, x.z, x.w};
             unsigned u[4];
 #pragma unroll
@@ -160,29 +161,64 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
                 const short sh = (short)(int)__fmul_rn(v[k], 511.0f);       // C float->short: truncation toward zero
                 u[k] = ((unsigned)(sh + 512)) & 0x3FFu;
             }
-            uint8_t *o = packed + qd * 5;
-            o[0] = (uint8_t)((u[0] >> 8) | ((u[1] >> 8) << 2) | ((u[2] >> 8) << 4) | ((u[3] >> 8) << 6));
-            o[1] = (uint8_t)(u[0] & 0xFF);
-            o[2] = (uint8_t)(u[1] & 0xFF);
-            o[3] = (uint8_t)(u[2] & 0xFF);
-            o[4] = (uint8_t)(u[3] & 0xFF);
+            b[0] = (u[0] >> 8) | ((u[1] >> 8) << 2) | ((u[2] >> 8) << 4) | ((u[3] >> 8) << 6);
+            b[1] = u[0] & 0xFF;
+            b[2] = u[1] & 0xFF;
+            b[3] = u[2] & 0xFF;
+            b[4] = u[3] & 0xFF;
+        };
+        // four quads (20 bytes = five 32-bit words) per lane and round
+        const int n_q4 = n_quads / 4;
+        for (int base = 0; base < n_q4; base += 32) {
+            const int q4 = base + lane;
+            float4 x[4];
+            if (q4 < n_q4) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) x[k] = load_quad(4 * q4 + k);
+            }
+            __syncwarp();
+            if (q4 < n_q4) {
+                uint32_t by[20];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    uint32_t b[5];
+                    pack_quad(x[k], b);
+#pragma unroll
+                    for (int j = 0; j < 5; j++) by[5 * k + j] = b[j];
+                }
+                uint32_t *o = reinterpret_cast<uint32_t *>(packed + q4 * 20);
+#pragma unroll
+                for (int j = 0; j < 5; j++) o[j] = by[4 * j] | (by[4 * j + 1] << 8) | (by[4 * j + 2] << 16) | (by[4 * j + 3] << 24);
+            }
         }
-        __syncthreads();
+        __syncwarp();
+        {   // the last one to three quads of a ragged tile
+            const int qd = 4 * n_q4 + lane;
+            float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (qd < n_quads) x = load_quad(qd);
+            __syncwarp();
+            if (qd < n_quads) {
+                uint32_t b[5];
+                pack_quad(x, b);
+#pragma unroll
+                for (int j = 0; j < 5; j++) packed[qd * 5 + j] = (uint8_t)b[j];
+            }
+        }
+        __syncwarp();
         char *dst = row0 + samp0 / 4 * 5;
-        const long n_bytes = n_quads * 5;
+        const int n_bytes = n_quads * 5;
         if (((reinterpret_cast<uintptr_t>(dst) | (uintptr_t)n_bytes) & 15) == 0) {
-            for (long i = threadIdx.x; i < n_bytes / 16; i += TX_THREADS)
-                reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(packed)[i];
+            for (int i = lane; i < n_bytes / 16; i += 32) reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(packed)[i];
         } else {
-            for (long i = threadIdx.x; i < n_bytes; i += TX_THREADS) dst[i] = (char)packed[i];
+            for (int i = lane; i < n_bytes; i += 32) dst[i] = (char)packed[i];
         }
     } else {
         float *dst = reinterpret_cast<float *>(row0) + samp0;
-        if (((reinterpret_cast<uintptr_t>(dst) & 15) | (n_samp & 3)) == 0) {
-            for (int i = threadIdx.x; i < (int)(n_samp / 4); i += TX_THREADS) reinterpret_cast<float4 *>(dst)[i] = load_quad(i);
+        if (((reinterpret_cast<uintptr_t>(dst) & 15) | (uintptr_t)(n_samp & 3)) == 0) {
+            for (int i = lane; i < n_samp / 4; i += 32) reinterpret_cast<float4 *>(dst)[i] = load_quad(i);
         } else {
             const int spg = TX_GROUP * sps;
-            for (int i = threadIdx.x; i < (int)n_samp; i += TX_THREADS) dst[i] = tile[(i / spg) * gstride + i % spg];
+            for (int i = lane; i < n_samp; i += 32) dst[i] = tile[(i / spg) * gstride + i % spg];
         }
     }
 }
@@ -207,23 +243,17 @@ int launch_bpsk_tx(const uint32_t *bits, long pitch_words, const uint64_t *hist_
     if (n_sym <= 0 || n_channels <= 0) return SFE_OK;
     const int M = (n_taps + sps - 1) / sps;
     const int MT = M <= 4 ? 4 : M <= 8 ? 8 : M <= 12 ? 12 : M <= 16 ? 16 : M <= 24 ? 24 : 32;
-    // symbols per CTA: as many as keep tile + packed copy under TX_TILE_BYTES, whole groups of 4 threads' worth
-    const int gstride = TX_GROUP * sps + 2;
-    const size_t per_group = sizeof(float) * gstride + (size_t)TX_GROUP * sps / 4 * 5 + 8;
-    int n_groups = (int)(TX_TILE_BYTES / per_group);
-    if (n_groups > TX_SYM_MAX / TX_GROUP) n_groups = TX_SYM_MAX / TX_GROUP;
-    n_groups = n_groups / 4 * 4;
-    if (n_groups < 4) n_groups = 4;
-    while (n_groups > 4 && (long)(n_groups / 2) * TX_GROUP >= n_sym) n_groups /= 2;   // short calls: no empty threads
-    n_groups = (n_groups + 3) / 4 * 4;
-    const int sym_cta = n_groups * TX_GROUP;
-    const size_t smem = sizeof(float) * ((size_t)sps * MT + (size_t)n_groups * gstride) + (size_t)sym_cta * sps / 4 * 5 + 32;
+    // a warp's tile is 32 groups of 16 sps + 2 floats; two warps per CTA unless the tiles get large (the taps are per CTA)
+    const size_t warp_tile = sizeof(float) * 32 * (size_t)(TX_GROUP * sps + 2);
+    const long n_warps = (n_sym + TX_WSYM - 1) / TX_WSYM;
+    int W = warp_tile <= 40 * 1024 ? 2 : 1;
+    if (W > n_warps) W = (int)n_warps;
+    const size_t smem = sizeof(float) * (size_t)sps * MT + W * warp_tile;
     auto kern = MT == 4 ? bpsk_tx_kernel<4> : MT == 8 ? bpsk_tx_kernel<8> : MT == 12 ? bpsk_tx_kernel<12> : MT == 16 ? bpsk_tx_kernel<16>
                 : MT == 24 ? bpsk_tx_kernel<24> : bpsk_tx_kernel<32>;
     if (!SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
-    dim3 grid((unsigned)((n_sym + sym_cta - 1) / sym_cta), (unsigned)n_channels);
-    kern<<<grid, TX_THREADS, smem, st>>>(bits, pitch_words, hist_old, n_hist, n_sym, sps, sym_cta, taps, n_taps, amp, out_dac10, out,
-                                         out_pitch_bytes);
+    dim3 grid((unsigned)((n_warps + W - 1) / W), (unsigned)n_channels);
+    kern<<<grid, 32 * W, smem, st>>>(bits, pitch_words, hist_old, n_hist, n_sym, sps, taps, n_taps, amp, out_dac10, out, out_pitch_bytes);
     bpsk_tx_hist_kernel<<<(n_channels + 127) / 128, 128, 0, st>>>(bits, pitch_words, hist_old, hist_new, n_sym, n_channels);
     count_launch(2);
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
