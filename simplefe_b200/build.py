@@ -55,7 +55,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
             else:
                 # host-only schedule code: as-written IEEE single precision, no FMA contraction
                 cmd = [nvcc, "-O2", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off",
-                       "-Xcompiler", "-fvisibility=hidden", "-x", "c++", "-c", s, "-o", o]
+                       "-Xcompiler", "-fvisibility=hidden",
+                       # the schedule walk is one tight float loop: pin its alignment, or its speed depends on what else is linked
+                       "-Xcompiler", "-falign-functions=64", "-Xcompiler", "-falign-loops=32", "-x", "c++", "-c", s, "-o", o]
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for src, p in procs:

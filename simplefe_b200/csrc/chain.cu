@@ -12,7 +12,9 @@
 //     host-generated float32 schedule).
 // Stream state (input history per stage, resampler phase) is carried across calls so a stream may
 // be fed in arbitrary pieces.
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <map>
 #include <string>
@@ -673,7 +675,10 @@ extern "C" int sfe_chain_process_dev(sfe_chain *c, const void *d_in, long n_in, 
         return SFE_ERR_ARG;
     }
     if (!SFE_CUDA(cudaSetDevice(c->dev))) return SFE_ERR_CUDA;
+    static const bool trace = getenv("SFE_TRACE_HOST") != nullptr;   // host time of the three parts of a call, on stderr
+    const auto t0 = std::chrono::steady_clock::now();
     plan_call(c, n_in);
+    const auto t1 = std::chrono::steady_clock::now();
     const long no = c->ops.back().n_out;
     if (n_out) *n_out = no;
     if (out_pitch < no) {
@@ -683,8 +688,16 @@ extern "C" int sfe_chain_process_dev(sfe_chain *c, const void *d_in, long n_in, 
     cudaStream_t st = (cudaStream_t)stream;
     int rc = upload_schedules(c, st);
     if (rc != SFE_OK) return rc;
+    const auto t2 = std::chrono::steady_clock::now();
     rc = run_ops(c, c->ws[0], 0, c->S, d_in, in_pitch, d_out, out_pitch, st);
     if (rc != SFE_OK) return rc;
+    if (trace) {
+        const auto t3 = std::chrono::steady_clock::now();
+        auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+            return std::chrono::duration<double, std::micro>(b - a).count();
+        };
+        fprintf(stderr, "sfe host trace: schedule %.0f us, upload %.0f us, launches %.0f us\n", us(t0, t1), us(t1, t2), us(t2, t3));
+    }
     c->cur ^= 1;
     return SFE_OK;
 }

@@ -27,23 +27,29 @@ int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t 
     out.resize(at + (size_t)(out_len > n_out ? out_len - n_out : 0));
     SchedEntry *dst = out.data() + at;
     const int32_t base32 = (int32_t)base;
+    // state lives in locals inside the loop (the only loop-carried dependency is t = tf + step); written back after it
+    int pos = st.pos;
+    float mu = st.mu;
+    bool held = st.held;
     for (;;) {
         const float tf = t;
-        int pos = (int)tf;                             // floorf(t) without the libm call: truncate, then fix t < 0
-        if ((float)pos > tf) pos--;
-        st.pos = pos;                                  // decimate.cxx:106
-        st.mu = tf - (float)pos;                       // decimate.cxx:107
+        pos = (int)tf;                                 // floorf(t) without the libm call: truncate, then fix t < 0
+        if ((float)pos > tf) pos--;                    // decimate.cxx:106
+        mu = tf - (float)pos;                          // decimate.cxx:107
         // n0 = pos / up and n1 = (pos + 1) / up (C truncating division, decimate.cxx:109-113) are only compared
         // with n_in: pos / up >= n_in  <=>  pos >= n_in * up for any sign of pos, so the walk needs no division
         if (pos >= lim || n_out >= out_len) break;     // decimate.cxx:115
         if (pos + 1 >= lim) {                          // decimate.cxx:118-121
-            st.held = true;
+            held = true;
             break;
         }
-        *dst++ = SchedEntry{base32 + pos, st.mu};
+        *dst++ = SchedEntry{base32 + pos, mu};
         n_out++;
         t = tf + step;                                 // decimate.cxx:124
     }
+    st.pos = pos;
+    st.mu = mu;
+    st.held = held;
     out.resize((size_t)(dst - out.data()));
     st.pos -= n_in * up;                               // decimate.cxx:127
     return n_out;
