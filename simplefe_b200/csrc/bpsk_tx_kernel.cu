@@ -9,11 +9,12 @@
 // computed here straight from the packed bits; the float waveform never leaves the chip when the caller asks
 // for DAC words.  The kernel is bound by its own output stream (12.5 bytes per symbol at sps = 10).
 //
-// Mapping: a warp owns 512 consecutive symbols of one channel, a thread 16 of them.  The thread derives the symbol signs of
+// Mapping: a warp owns 256 consecutive symbols of one channel, a thread 8 of them (16 was measured slower: the tile per
+// thread limits the resident warps).  The thread derives the symbol signs of
 // its group once, from one 64-bit window of the bit stream, as +-1.0f registers, and then walks the phases
 // r = 0 .. sps-1: the ~12 pre-scaled taps h[r + m*sps] of the phase come from shared memory with 128-bit loads, every
-// tap and output costs one FFMA, and the 16 results go to the warp's own shared-memory tile in time order (group stride
-// 16*sps + 2 words: 2-way instead of 32-way bank conflicts).  The warp then packs its tile (DAC words: in place) and
+// tap and output costs one FFMA, and the 8 results go to the warp's own shared-memory tile in time order (group stride
+// 8*sps + 2 words: 2-way instead of 32-way bank conflicts).  The warp then packs its tile (DAC words: in place) and
 // stores 128-bit words.  Tiles are warp-private, so warps only meet at __syncwarp: while one warp stores, the others
 // compute (with CTA-wide tiles 22 % of the stall samples were the barrier between the two passes).
 #include "kernels.h"
@@ -22,7 +23,8 @@ namespace sfe {
 
 namespace {
 
-constexpr int TX_GROUP = 16;       // symbols per thread
+constexpr int TX_GROUP = 8;        // symbols per thread
+constexpr int TX_WBIT = 64 - TX_GROUP;   // window bit of the thread's first symbol (bit 63 = its last)
 constexpr int TX_WSYM = 32 * TX_GROUP;   // symbols per warp
 constexpr int TX_MAXM = 32;        // taps per phase, at most (n_taps <= 32 * sps)
 constexpr int TX_MAXW = 4;         // warps per CTA, at most
@@ -74,7 +76,7 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
 
     const long s_first = s0 + (long)lane * TX_GROUP;
     if (s_first < n_sym) {
-        // window: bit 63 = symbol s_first + 15, ..., bit 0 = symbol s_first - 48
+        // window: bit 63 = the thread's last symbol (s_first + TX_GROUP - 1), bit TX_WBIT = s_first, bit 0 = s_first - TX_WBIT
         const uint64_t w = bits_window(cur, hw, s_first + TX_GROUP - 1, n_sym);
         float *trow = tile + lane * gstride;
         if (s_first - (M - 1) >= -(long)n_hist && s_first + TX_GROUP <= n_sym) {
@@ -86,7 +88,7 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
             const uint32_t wl = (uint32_t)w, wh = (uint32_t)(w >> 32);
 #pragma unroll
             for (int d = 0; d < TX_GROUP + MT - 1; d++) {
-                const int bit = 49 - MT + d;                               // compile-time position in the window
+                const int bit = TX_WBIT + 1 - MT + d;                               // compile-time position in the window
                 const uint32_t word = bit < 32 ? wl : wh;
                 sg[d] = __uint_as_float(0x3F800000u | ((word << (31 - (bit & 31))) & 0x80000000u));
             }
@@ -123,7 +125,7 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
                     for (int i = 0; i < TX_GROUP; i++) {
                         const long sm = s_first + i - m;                       // symbol s - m
                         const bool valid = sm >= -(long)n_hist && sm < n_sym;  // before the first symbol: zero state
-                        const uint32_t sign = (uint32_t)((w >> (48 + i - m)) & 1ull) << 31;   // a set bit sends -A (bpsk.cxx:150)
+                        const uint32_t sign = (uint32_t)((w >> (TX_WBIT + i - m)) & 1ull) << 31;   // a set bit sends -A (bpsk.cxx:150)
                         acc[i] += valid ? __uint_as_float(hb ^ sign) : 0.f;
                     }
                 }
@@ -246,7 +248,7 @@ int launch_bpsk_tx(const uint32_t *bits, long pitch_words, const uint64_t *hist_
     // a warp's tile is 32 groups of 16 sps + 2 floats; two warps per CTA unless the tiles get large (the taps are per CTA)
     const size_t warp_tile = sizeof(float) * 32 * (size_t)(TX_GROUP * sps + 2);
     const long n_warps = (n_sym + TX_WSYM - 1) / TX_WSYM;
-    int W = warp_tile <= 40 * 1024 ? 2 : 1;
+    int W = warp_tile <= 20 * 1024 ? 4 : warp_tile <= 40 * 1024 ? 2 : 1;
     if (W > n_warps) W = (int)n_warps;
     const size_t smem = sizeof(float) * (size_t)sps * MT + W * warp_tile;
     auto kern = MT == 4 ? bpsk_tx_kernel<4> : MT == 8 ? bpsk_tx_kernel<8> : MT == 12 ? bpsk_tx_kernel<12> : MT == 16 ? bpsk_tx_kernel<16>
