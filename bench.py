@@ -305,7 +305,7 @@ def main():
         n_out = step()
     barrier()
     # every third step is bracketed with events for the roofline; the others run as a caller's would (a bracketed
-    # step costs two event records and keeps the state carry from overlapping the main kernel's last wave)
+    # step costs two event records and keeps the state carry from running beside the main kernel)
     ch.profile(args.profile_every)
     sampler = ClockSampler(local_rank)
     if rank == 0:

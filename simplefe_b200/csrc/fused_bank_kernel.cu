@@ -279,7 +279,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     __shared__ __align__(8) uint64_t bars[WARPS * NST];
 
     // The state carry that follows in the stream (save_tail) reads the same inputs and writes a buffer this kernel never
-    // touches: once the last wave of CTAs is resident it may start, filling the SMs this kernel's tail leaves idle.
+    // touches: it may start as soon as every CTA of this grid has got here (one CTA per SM: right away) and runs beside it.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
