@@ -562,7 +562,10 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
             const int row_hi = __reduce_max_sync(0xffffffffu, valid ? row : 0);
             const int off = row_hi - row;
             int M = __reduce_max_sync(0xffffffffu, valid ? off + J + d : 0);
-            M = min((M + 1) & ~1, p.grp_rows);                             // two samples per round; the launcher sized the table for 3 steps + J
+            // two samples per round.  Consecutive outputs of a float32 time walk are at most ceil(step) + 1 grid positions
+            // apart (decimate.cxx:124, also across a call seam and a held-over output), and the launcher sized the table
+            // for (LS_G - 1) such gaps plus one window, so the clamp never cuts a live tap.
+            M = min((M + 1) & ~1, p.grp_rows);
             const float *t0 = tp + ph0 * J, *t1 = tp + ph1 * J;
             const float w0 = 1.0f - mu;
             __syncwarp();                                                  // the previous run's readers are done
@@ -597,7 +600,7 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
         }
     } else {
         f32x2 *cw = cb + warp * JC;
-    #pragma unroll
+#pragma unroll
         for (int q = 0; q < LS_KPW; q++) {
             res[q] = 0ull;
             const long k = k0 + warp + LS_WARPS * q;
