@@ -54,6 +54,7 @@ struct Op {
     SchedEntry *h_sched = nullptr;   // pinned staging copy of the schedule
     size_t h_sched_cap = 0;
     cudaEvent_t h_sched_done = nullptr;
+    void *reg_ptr = nullptr;         // storage of sched.e while it is registered as pinned memory (copied from in place)
     // decimating FIR
     int D = 0, QLP = 0;
     float *d_gp = nullptr;
@@ -215,6 +216,19 @@ void plan_call(sfe_chain *c, long n_in)
             if (op.n_out > 0 && !op.sched.uniform) op.bad_sched = true;
         } else {
             // the closed-form kernels only need the summary; the generic kernel wants every (pos, mu)
+            if (op.kind == OP_POLY) {
+                // The entry list is copied to the device from where the walk writes it (its storage is registered as pinned
+                // memory, upload_schedules): wait for the previous copy, and grow the storage here, unregistered -- never
+                // inside the walk.
+                if (op.h_sched_done) cudaEventSynchronize(op.h_sched_done);
+                const size_t calls = (size_t)(n / (op.blk > 0 ? op.blk : 1)) + 2;
+                const size_t bound = (size_t)((double)n / (double)op.rate * 1.01) + 4 * calls + (size_t)((double)op.blk / (double)op.rate) + 64;
+                if (op.sched.e.capacity() < bound) {
+                    if (op.reg_ptr) cudaHostUnregister(op.reg_ptr);
+                    op.reg_ptr = nullptr;
+                    op.sched.e.reserve(2 * bound);
+                }
+            }
             walk_batch(op.ws, op.up, op.blk, op.rate, n, op.sched, op.kind == OP_POLY);
             op.n_out = (long)op.sched.count;
         }
@@ -386,6 +400,21 @@ int upload_schedules(sfe_chain *c, cudaStream_t st)
             op.d_sched_cap = 0;
             if (!SFE_CUDA(cudaMalloc(&op.d_sched, need * 2))) return SFE_ERR_CUDA;
             op.d_sched_cap = need * 2;
+        }
+        if (!op.h_sched_done && !SFE_CUDA(cudaEventCreateWithFlags(&op.h_sched_done, cudaEventDisableTiming))) return SFE_ERR_CUDA;
+        // straight from the vector the walk filled, once its storage is registered (plan_call keeps it from moving)
+        void *hp = op.sched.e.data();
+        if (op.reg_ptr != hp) {
+            if (op.reg_ptr) cudaHostUnregister(op.reg_ptr);
+            op.reg_ptr = nullptr;
+            if (cudaHostRegister(hp, op.sched.e.capacity() * sizeof(SchedEntry), cudaHostRegisterDefault) == cudaSuccess) op.reg_ptr = hp;
+            else cudaGetLastError();   // refused: the staging copy below still works
+        }
+        if (op.reg_ptr == hp) {
+            if (!SFE_CUDA(cudaMemcpyAsync(op.d_sched, hp, need, cudaMemcpyHostToDevice, st)) ||
+                !SFE_CUDA(cudaEventRecord(op.h_sched_done, st)))
+                return SFE_ERR_CUDA;
+            continue;
         }
         // through a pinned staging buffer: the copy is a real asynchronous DMA instead of a staged pageable one.  The
         // buffer may only be rewritten once its previous copy has completed.
@@ -597,6 +626,7 @@ extern "C" void sfe_chain_destroy(sfe_chain *c)
         cudaFree(op.d_gp);
         cudaFree(op.d_bmat);
         cudaFree(op.d_sched);
+        if (op.reg_ptr) cudaHostUnregister(op.reg_ptr);
         if (op.h_sched) cudaFreeHost(op.h_sched);
         if (op.h_sched_done) cudaEventDestroy(op.h_sched_done);
         for (auto &kv : op.d_tables) cudaFree(kv.second);
