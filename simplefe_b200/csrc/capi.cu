@@ -279,7 +279,7 @@ struct sfe_polyphase {
     int out_cap = 0;
     SchedEntry *d_sched = nullptr;
     int sched_cap = 0;
-    std::vector<SchedEntry> sched;
+    EntryVec sched;
     cudaStream_t st = nullptr;
 };
 

@@ -7,7 +7,7 @@
 namespace sfe {
 
 int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t base_in,
-              std::vector<SchedEntry> &out)
+              EntryVec &out)
 {
     int n_out = 0;
     const int64_t base = base_in * (int64_t)up;
@@ -33,6 +33,51 @@ int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t 
     bool held = st.held;
     for (;;) {
         const float tf = t;
+        // Closed-form run.  Inside one binade [2^e, 2^(e+1)) every time value is a multiple of u = 2^(e-23), and
+        // RN(t + step) - t is the same multiple INC of u for every t whose sum stays representable at that ulp (step
+        // rounded to the ulp; a tie only makes the first addition differ, hence the three probes).  So the next values
+        // are X*u with X += INC in integers: no floating-point dependency chain (the reference's recurrence costs one
+        // add latency per output), identical bits.  Anything else -- t < 1, the addition that leaves the binade, the
+        // end-of-call checks -- goes through the reference's own sequence below.
+        if (tf >= 1.0f && tf < 4194304.0f) {
+            uint32_t b0, b1, b2, b3;
+            const float t1 = tf + step, t2 = t1 + step, t3 = t2 + step;
+            memcpy(&b0, &tf, 4);
+            memcpy(&b1, &t1, 4);
+            memcpy(&b2, &t2, 4);
+            memcpy(&b3, &t3, 4);
+            if ((b3 >> 23) == (b0 >> 23)) {            // all four in the binade of tf
+                const int e = (int)(b0 >> 23) - 127;
+                const uint32_t X0 = (b0 & 0x7FFFFFu) | 0x800000u, X1 = (b1 & 0x7FFFFFu) | 0x800000u;
+                const uint32_t X2 = (b2 & 0x7FFFFFu) | 0x800000u, X3 = (b3 & 0x7FFFFFu) | 0x800000u;
+                const uint32_t INC = X1 - X0;
+                if (INC > 0 && X2 - X1 == INC && X3 - X2 == INC) {
+                    const int sh = 23 - e;
+                    const uint32_t fm = (1u << sh) - 1u;
+                    uint32_t ub = (uint32_t)(e - 23 + 127) << 23;
+                    float u;
+                    memcpy(&u, &ub, 4);
+                    // length of the run: (a) the sum from X must still round at this ulp, X + INC + 1 <= 2^24;
+                    // (b) the reference's end-of-call checks stay false, (X >> sh) + 1 < lim; (c) room for outputs
+                    int64_t n_run = (int64_t)((0xFFFFFFu - X0) / INC);
+                    const int64_t L = lim > 1 ? ((lim - 1) << sh) : 0;          // X < L  <=>  (X >> sh) + 1 < lim
+                    const int64_t n_b = L > (int64_t)X0 ? (L - (int64_t)X0 + INC - 1) / INC : 0;
+                    if (n_b < n_run) n_run = n_b;
+                    if (out_len - n_out < n_run) n_run = out_len - n_out;
+                    if (n_run > 0) {
+                        const int nr = (int)n_run;
+                        for (int j = 0; j < nr; j++) {                           // no dependency between iterations
+                            const uint32_t X = X0 + (uint32_t)j * INC;
+                            dst[j] = SchedEntry{base32 + (int32_t)(X >> sh), (float)(X & fm) * u};
+                        }
+                        dst += nr;
+                        n_out += nr;
+                        t = (float)(X0 + (uint32_t)nr * INC) * u;                // exact: at most 2^24
+                        continue;
+                    }
+                }
+            }
+        }
         pos = (int)tf;                                 // floorf(t) without the libm call: truncate, then fix t < 0
         if ((float)pos > tf) pos--;                    // decimate.cxx:106
         mu = tf - (float)pos;                          // decimate.cxx:107
@@ -72,8 +117,8 @@ void walk_batch(WalkState &st, int up, int blk, float rate, int64_t n_in, Schedu
     if (stepf != floorf(stepf)) {
         // fractional step: (pos, mu, held) never repeats, so memoising calls only costs allocations; walk straight
         // into the entry list.  Such a schedule is never closed-form (mu != 0 somewhere).
-        std::vector<SchedEntry> scratch;
-        std::vector<SchedEntry> &dst = want_entries ? s.e : scratch;
+        EntryVec scratch;
+        EntryVec &dst = want_entries ? s.e : scratch;
         if (want_entries) dst.reserve((size_t)((double)n_in / (double)rate) + (size_t)(n_in / blk) * 2 + 8);
         for (int64_t off = 0; off < n_in; off += blk) {
             const int n = (int)((n_in - off) < blk ? (n_in - off) : blk);

@@ -9,7 +9,9 @@
 #pragma once
 #include <cstdint>
 #include <map>
+#include <memory>
 #include <tuple>
+#include <utility>
 #include <vector>
 
 namespace sfe {
@@ -27,10 +29,19 @@ struct SchedEntry {
     float mu;             // out = s(pos)*(1-mu) + mu*s(pos+1)
 };
 
+// entry lists are filled by raw stores right after a resize(): an allocator whose default construction is a no-op keeps
+// resize() from zero-filling memory that is about to be overwritten
+template <class T> struct DefaultInitAlloc : std::allocator<T> {
+    template <class U> struct rebind { typedef DefaultInitAlloc<U> other; };
+    template <class U> void construct(U *p) noexcept { ::new (static_cast<void *>(p)) U; }
+    template <class U, class... A> void construct(U *p, A &&...a) { ::new (static_cast<void *>(p)) U(std::forward<A>(a)...); }
+};
+typedef std::vector<SchedEntry, DefaultInitAlloc<SchedEntry>> EntryVec;
+
 // what one reference process() call does from a given state: memoised, because for integral steps the
 // state (pos, mu, held) cycles through a handful of values and a batch is thousands of identical calls
 struct CallMemo {
-    std::vector<SchedEntry> e;  // entries relative to the call's first sample (base_in = 0)
+    EntryVec e;                 // entries relative to the call's first sample (base_in = 0)
     WalkState after;
     bool mu0 = true;            // all mu == 0
     bool arith = true;          // positions form an arithmetic progression
@@ -38,7 +49,7 @@ struct CallMemo {
 };
 
 struct Schedule {
-    std::vector<SchedEntry> e;  // one per output, in output order (empty in summary mode)
+    EntryVec e;                 // one per output, in output order (empty in summary mode)
     int64_t count = 0;          // number of outputs of the batch
     bool uniform = false;       // all mu == 0 and pos = pos0 + k*step
     int64_t pos0 = 0, step = 0;
@@ -51,7 +62,7 @@ struct Schedule {
 // One reference process() call: appends the outputs of a call with n_in samples whose first
 // sample sits at batch offset `base_in`; updates st.  Returns the number of outputs appended.
 int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t base_in,
-              std::vector<SchedEntry> &out);
+              EntryVec &out);
 
 // A batch of n_in samples fed as ceil(n_in/blk) calls of blk samples, out_len = floor(blk/rate)+2.
 // want_entries = false (summary mode): only count / uniform / pos0 / step are produced -- all that the

@@ -74,7 +74,7 @@ int main(int argc, char** argv) {
     if (s2.count != (long)s.e.size() || s2.uniform != s.uniform || s2.pos0 != s.pos0 || s2.step != s.step || !s2.e.empty() ||
         st2.pos != st.pos || st2.mu != st.mu || st2.held != st.held) { printf("SUMMARY MISMATCH\n"); return 1; }
     // and with the unmemoised reference walk, call by call
-    { static sfe::WalkState st3; std::vector<sfe::SchedEntry> e3; int ol = (int)floorf((float)blk / rate) + 2;
+    { static sfe::WalkState st3; sfe::EntryVec e3; int ol = (int)floorf((float)blk / rate) + 2;
       for (long off = 0; off < n; off += blk) sfe::walk_call(st3, up, (int)((n - off) < blk ? (n - off) : blk), ol, rate, off, e3);
       if (e3.size() != s.e.size()) { printf("MEMO MISMATCH\n"); return 1; }
       for (size_t k = 0; k < e3.size(); k++) if (e3[k].pos != s.e[k].pos || e3[k].mu != s.e[k].mu) { printf("MEMO MISMATCH\n"); return 1; } }
@@ -98,3 +98,19 @@ int main(int argc, char** argv) {
             for rep in range(3):
                 want = len(o.stream(x, rate))
                 assert int(out[rep].split()[0]) == want, (cls, up, blk, rate, rep, out[rep], want)
+
+
+def test_schedule_closed_form_runs_match_the_sequential_walk():
+    """csrc/schedule.cpp replaces stretches of the reference's t += step recurrence (decimate.cxx:124) by integer
+    arithmetic on the mantissa inside one binade; tests/cpp/walk_diff.cxx checks it bit for bit (positions, mu, carried
+    state, held-over outputs) against the plain recurrence over random rates, upsampling factors and ragged calls"""
+    import subprocess
+    import tempfile
+    csrc = os.path.join(ROOT, "simplefe_b200", "csrc")
+    with tempfile.TemporaryDirectory() as td:
+        exe = os.path.join(td, "walk_diff")
+        subprocess.run(["g++", "-O2", "-ffp-contract=off", "-std=c++17", "-I", csrc, os.path.join(ROOT, "tests", "cpp", "walk_diff.cxx"),
+                        os.path.join(csrc, "schedule.cpp"), "-o", exe], check=True)
+        for seed in (1, 2, 3):
+            r = subprocess.run([exe, str(seed), "1500"], capture_output=True, text=True)
+            assert r.returncode == 0 and r.stdout.startswith("ok:"), r.stdout
