@@ -671,9 +671,15 @@ int launch_poly_generic(const PolyParams &p_in, cudaStream_t st)
     // many streams sharing the schedule: lane-per-stream flavour (K2s)
     static const bool no_lanes = getenv("SFE_POLY_NO_LANES") != nullptr;   // tuning hook
     if (!p.exact && !p.in_real && p.n_streams >= 16 && tap_bytes <= 32 * 1024 && !no_lanes) {
-        static const long tile_kb = getenv("SFE_POLY_LANES_TILE_KB") ? atol(getenv("SFE_POLY_LANES_TILE_KB")) : 40;   // tuning hook (64: 1.32 ms, 40: 1.26 ms, 24: 1.41 ms on cfg 4 stage a)
-        const long cap_s = (tile_kb * 1024) / (LS_PITCH * 8);               // samples of span per CTA
+        // tile: 40 KB when that still holds whole runs for every warp (more CTAs per SM: 1.26 instead of 1.32 ms on cfg 4
+        // stage a; 24 KB: 1.41 ms), else 64 KB (large steps: few outputs fit, and below 8 the tiled generic kernel takes over)
+        static const long tile_kb = getenv("SFE_POLY_LANES_TILE_KB") ? atol(getenv("SFE_POLY_LANES_TILE_KB")) : 0;   // tuning hook
+        long cap_s = ((tile_kb > 0 ? tile_kb : 40) * 1024) / (LS_PITCH * 8);   // samples of span per CTA
         long kl = (long)((double)(cap_s - p.jp - 8) / (per_out * 1.01 + 1e-9));
+        if (tile_kb <= 0 && kl < LS_WARPS * LS_G) {
+            cap_s = (64 * 1024) / (LS_PITCH * 8);
+            kl = (long)((double)(cap_s - p.jp - 8) / (per_out * 1.01 + 1e-9));
+        }
         if (kl > LS_KT) kl = LS_KT;
         kl = kl >= LS_WARPS * LS_G ? kl / (LS_WARPS * LS_G) * (LS_WARPS * LS_G) : kl / LS_WARPS * LS_WARPS;   // whole runs of LS_G per warp
         if (kl >= 8) {
