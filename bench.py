@@ -3,16 +3,20 @@
 
 Workload (BASELINE.json configs[4], SURVEY.md 8-d cfg 5): 1024 independent int16 IQ streams x 2^20
 samples through blkconv(255 taps, FFT 4096) -> decimate(128 taps, /8) -> resample(512 taps, L=24,
-rate 625/24), one shared filter set, streams partitioned over the N GPUs (no collective: the path
-never exchanges data between streams).  Metric: Msamples/s, one sample = one complex input sample.
+rate 625/24), one shared filter set.  The 1024 streams are SPLIT over the N GPUs (strong scaling:
+1024 / 512 / 256 / 128 streams per GPU at N = 1 / 2 / 4 / 8); there is no collective:
+the path never exchanges data between streams.  Metric: Msamples/s, one sample = one complex input sample.
 
-    python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+    python bench.py [--gpus N --steps K --warmup W] [--impl reference] [--config cfg1..cfg5]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 One JSON line on stdout (rank 0).  `value` = device-resident throughput (CUDA events, max over
 ranks); `e2e` = the same through the host-buffer C-ABI call (pinned host in, pinned host out,
-copies inside the timed region); `roofline` = the dominant kernel against the measured HBM peak;
-`cpu_baseline` = the reference's own CPU code (oracle/_ref) on this box's host cores.
+copies inside the timed region) next to the box's measured concurrent H2D ceiling; `roofline` = the
+dominant kernel against the measured HBM peak; `parity` = a sample of the output rows of every rank
+against the reference's own CPU code (outside the timed region); `cpu_baseline` = that CPU code timed
+on this box's host cores; `weak` (N > 1) = the secondary figure with 1024 streams on every GPU.
+`--config cfg1..cfg4` runs the other BASELINE.json configs through the same harness (same keys).
 """
 from __future__ import annotations
 
@@ -133,16 +137,43 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic():
-    """dram bytes per launch of the dominant kernel from the committed ncu capture, if any"""
+def ncu_traffic(name, plan=None):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture of THIS build's kernel, if any
+    (profiles/dominant_kernel_traffic.json is regenerated by scripts/ncu_traffic.py from an `ncu --set full` capture;
+    an entry is used only when its workload and kernel plan match the run)"""
     try:
         d = json.load(open(os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")))
-        return d
+        e = d.get(name) if isinstance(d.get(name), dict) else (d if name == "cfg5" and "dram_bytes_per_launch" in d else None)
+        if e and plan and e.get("plan") and e["plan"] != plan:
+            return {"dram_bytes_per_launch": None, "source": f"stale: capture was of plan {e['plan']}"}
+        return e
     except Exception:
         return None
 
 
 # ---------------------------------------------------------------------------------------------------
+# workloads: BASELINE.json configs (SURVEY.md 8-d).  cfg5 is the headline; cfg1..cfg4 run through the same harness.
+FLAG_EXACT, FLAG_NO_FUSE, FLAG_NO_TENSOR, FLAG_NO_BANK = 1, 2, 4, 8
+EB = {F.IN_I16: 4, F.IN_U8: 2, F.IN_F32: 8}
+WORKLOADS = {
+    # name: (fixture, streams batched, samples, streams as worded, samples as worded, text)
+    "cfg1": ("cfg1", 256, 1 << 20, 1, 1 << 20, "cfg1: blkconv 255 taps, FFT 4096 on complex-float streams of 2^20 samples"),
+    "cfg2": ("cfg2", 1024, 1 << 20, 1, 10_000_000, "cfg2: decimate /8, 128-tap polyphase FIR on int16 IQ streams"),
+    "cfg3": ("cfg3", 1024, 1 << 20, 1, 10_000_000, "cfg3: rational resample 10 MS/s -> 48 kS/s (L=3, M=625, 512 taps) on int16 IQ streams"),
+    "cfg4": ("cfg4", 256, 1_000_000, 1, 1_000_000, "cfg4: BPSK receive chain blkconv(111 RRC, FFT 2048) -> decimate(31 taps, rate 2.5003) -> "
+                                                     "resample(31 taps, L=4, rate 1.77), fractional rates"),
+    "cfg5": ("cfg5", 1024, 1 << 20, 1024, 1 << 20, "cfg5: 1024 int16 IQ streams x 2^20 samples, blkconv(255 taps, FFT 4096) -> decimate(128 taps, /8) "
+                                                     "-> resample(512 taps, L=24, rate 625/24)"),
+}
+
+
+def bytes_alg_per_sample(name, cfg, N, n_out):
+    """first read of the input + final write of the output, per complex input sample"""
+    if name == "cfg5" and cfg["in_fmt"] == F.IN_I16:
+        return BYTES_ALG_PER_SAMPLE
+    return EB[cfg["in_fmt"]] + 8.0 * n_out / max(N, 1)
+
+
 def cpu_chain(cfg, iq, n_threads, fast=True):
     from oracle import oracle as O
     lib = O.load("auto", fast=fast)
@@ -159,36 +190,116 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+def cpu_build_note(lib, cfg):
+    b = lib.sfeo_build_flags().decode()
+    if cfg.get("blkconv") is not None:
+        b += " | blkconv's FFT = this repo's float Stockham shim (oracle/fftw_shim.cxx), NOT FFTW: the image has no libfftw3f"
+    return b
+
+
+def strong_cpu_fft(cfg, make_rows, budget_s=4.0):
+    """SURVEY.md 8-d 'strong CPU' yardstick for the FFT stage: scipy float32 pocketfft overlap-add of blkconv's stage
+    only (int16->float conversion included), vectorised over blocks, all host threads.  It bounds how much the
+    shim-backed reference build understates a CPU with a real FFT library."""
+    if cfg.get("blkconv") is None:
+        return None
+    try:
+        import scipy.fft as sfft
+    except Exception as ex:
+        return {"error": repr(ex)}
+    T = host_threads()
+    taps, nfft = cfg["blkconv"]
+    taps = np.asarray(taps, np.float32)
+    blk = nfft + 1 - len(taps)
+    Hf = sfft.rfft(np.concatenate([taps, np.zeros(nfft - len(taps), np.float32)])).astype(np.complex64)
+    N = cfg["N"]
+
+    def run(iq):
+        S = iq.shape[0]
+        if cfg["in_fmt"] == F.IN_I16:
+            x = iq.astype(np.float32) * np.float32(1.0 / 32767.0)
+        elif cfg["in_fmt"] == F.IN_U8:
+            x = (iq.astype(np.float32) - np.float32(128)) * np.float32(1.0 / 127.0)
+        else:
+            x = iq
+        x = np.ascontiguousarray(np.moveaxis(x, 2, 1)).reshape(2 * S, N)          # one real row per component
+        nb = (N + blk - 1) // blk
+        xb = np.zeros((2 * S, nb, nfft), np.float32)
+        xb.reshape(2 * S, nb * nfft)  # view check
+        pad = np.zeros((2 * S, nb * blk), np.float32)
+        pad[:, :N] = x
+        xb[:, :, :blk] = pad.reshape(2 * S, nb, blk)
+        Y = sfft.rfft(xb, axis=-1, workers=T)
+        Y *= Hf
+        yb = sfft.irfft(Y, n=nfft, axis=-1, workers=T)
+        out = np.zeros((2 * S, nb * blk + nfft), np.float32)
+        out[:, :nb * blk] = yb[:, :, :blk].reshape(2 * S, nb * blk)
+        tail = yb[:, :, blk:]
+        for j in range(nb):                                                       # overlap-add of the tails
+            out[:, (j + 1) * blk:(j + 1) * blk + nfft - blk] += tail[:, j]
+        return out[:, :N]
+
+    t0 = time.perf_counter()
+    run(make_rows(1))
+    t1 = time.perf_counter() - t0
+    S = int(max(1, min(4 * T, budget_s / max(t1, 1e-3))))
+    iq = make_rows(S)
+    t0 = time.perf_counter()
+    run(iq)
+    dt = time.perf_counter() - t0
+    return {"value": S * N / dt / 1e6, "unit": METRIC, "cores": T, "stage": "blkconv only (the chain's later stages excluded)",
+            "kind": "scipy.fft float32 pocketfft overlap-add, vectorised over blocks",
+            "sample": f"{S} streams x {N} samples, {dt:.2f} s"}
+
+
 def cpu_baseline(cfg, make_rows, budget_s=12.0):
     """The reference's CPU path on a bounded sample of the same workload, all host threads."""
     T = host_threads()
     N = cfg["N"]
     t1, _, lib = cpu_chain(cfg, make_rows(1), 1)            # one stream on one thread: calibration
     per_thread = max(1, int(budget_s / max(t1, 1e-3)))
-    S = int(min(cfg["S"], max(T, per_thread * T)))
+    S = int(min(max(cfg["S"], T), max(T, per_thread * T)))
     S = max(T, S // T * T) if S >= T else S
     iq = make_rows(S)
     dt, _, _ = cpu_chain(cfg, iq, T)
     v = S * N / dt / 1e6
-    return {"value": v, "unit": METRIC, "cores": T, "kind": lib.sfeo_kind().decode(),
-            "sample": f"{S} of {cfg['S']} streams x {N} samples, {T} threads, {dt:.2f} s; 1 thread: {N / t1 / 1e6:.2f} {METRIC}",
-            "build": lib.sfeo_build_flags().decode(), "one_thread_value": N / t1 / 1e6}
+    out = {"value": v, "unit": METRIC, "cores": T, "kind": lib.sfeo_kind().decode(),
+           "sample": f"{S} streams x {N} samples ({cfg['S']} in the workload), {T} threads, {dt:.2f} s; 1 thread: {N / t1 / 1e6:.2f} {METRIC}",
+           "build": cpu_build_note(lib, cfg), "one_thread_value": N / t1 / 1e6}
+    try:
+        sc = strong_cpu_fft(cfg, make_rows)
+        if sc is not None:
+            out["strong_cpu_fft"] = sc
+    except Exception as ex:
+        out["strong_cpu_fft"] = {"error": repr(ex)}
+    return out
+
+
+def host_rows(cfg, n_extra=8192):
+    """S distinct rows in the config's input format as windows of one long seeded base signal (cheap on the host)"""
+    rng = np.random.Generator(np.random.PCG64(cfg["seed"]))
+    v = np.clip(rng.normal(0.0, 0.25, size=(cfg["N"] + n_extra, 2)), -1, 1)
+    if cfg["in_fmt"] == F.IN_I16:
+        base = F._quant16(v)
+    elif cfg["in_fmt"] == F.IN_U8:
+        base = np.clip(np.round(v * 127.0) + 128, 0, 255).astype(np.uint8)
+    else:
+        base = v.astype(np.float32)
+
+    def make_rows(S):
+        return np.stack([base[(37 * s) % n_extra:(37 * s) % n_extra + cfg["N"]] for s in range(S)])
+    return make_rows
 
 
 # ---------------------------------------------------------------------------------------------------
-def run_reference(args, cfg, rank, world):
+def run_reference(args, name, cfg, rank, world):
     """--impl reference: the reference's own CPU implementation (oracle/_ref), rank 0 only."""
     if rank != 0:
         return
     T = host_threads()
-    rng = np.random.Generator(np.random.PCG64(cfg["seed"]))
-    base = F._quant16(np.clip(rng.normal(0.0, 0.25, size=(cfg["N"] + 4096, 2)), -1, 1))
-
-    def make_rows(S):
-        return np.stack([base[(37 * s) % 4096:(37 * s) % 4096 + cfg["N"]] for s in range(S)])
-
+    make_rows = host_rows(cfg)
     t1, _, lib = cpu_chain(cfg, make_rows(1), 1)
-    S = int(min(cfg["S"], max(T, int(8.0 / max(t1, 1e-3)) * T)))
+    S = int(min(max(cfg["S"], T), max(T, int(8.0 / max(t1, 1e-3)) * T)))
     S = max(T, S // T * T) if S >= T else S
     iq = make_rows(S)
     for _ in range(args.warmup):
@@ -202,23 +313,53 @@ def run_reference(args, cfg, rank, world):
         "impl": "reference", "metric": METRIC, "value": v, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(cfg, args.gpus),
+        "config": workload_config(name, cfg, args.gpus, args.scaling),
         "cpu_baseline": {"value": v, "unit": METRIC, "cores": T, "kind": lib.sfeo_kind().decode(),
-                         "sample": f"{S} of {cfg['S']} streams x {cfg['N']} samples per step, {T} threads",
-                         "build": lib.sfeo_build_flags().decode()},
+                         "sample": f"{S} streams x {cfg['N']} samples per step ({cfg['S']} in the workload), {T} threads",
+                         "build": cpu_build_note(lib, cfg)},
         "e2e": {"value": v, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(line)
 
 
-def workload_config(cfg, n_gpus, streams_per_gpu=None, scaling="weak"):
-    spg = streams_per_gpu if streams_per_gpu is not None else cfg["S"]
-    return {"workload": "cfg5: 1024 int16 IQ streams x 2^20 samples per GPU, blkconv(255 taps, FFT 4096) -> decimate(128 taps, /8) "
-                        "-> resample(512 taps, L=24, rate 625/24)",
-            "streams_total": spg * n_gpus, "samples_per_stream": cfg["N"], "streams_per_gpu": spg,
-            "partition": f"independent streams over {n_gpus} GPU(s) ({scaling}), no collective",
-            "l2": "inputs larger than L2 (no flush needed)"}
+def workload_config(name, cfg, n_gpus, scaling):
+    """identical in both arms (ours / reference): the driver compares the two `config` objects"""
+    S = cfg["S"]
+    return {"workload": WORKLOADS[name][5], "streams_total": S, "samples_per_stream": cfg["N"],
+            "streams_per_gpu": S // n_gpus if scaling == "strong" else S,
+            "partition": f"independent streams split over {n_gpus} GPU(s) ({scaling}), no collective",
+            "l2": "inputs larger than L2 (no flush needed)" if S * cfg["N"] * EB[cfg["in_fmt"]] // max(n_gpus, 1) > (256 << 20)
+                  else "L2 flushed between timed steps (write of a 256 MiB buffer)"}
+
+
+def device_rows(torch, cfg, S, N, dev, seed):
+    """synthetic rows generated on the device: N(0, 0.25^2) clipped, quantised to the config's input format"""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    fmt = cfg["in_fmt"]
+    dt = {F.IN_I16: torch.int16, F.IN_U8: torch.uint8, F.IN_F32: torch.float32}[fmt]
+    d_in = torch.empty((S, N, 2), dtype=dt, device=dev)
+    rows = max(1, (256 << 20) // (N * 2 * 4))
+    for s0 in range(0, S, rows):
+        blk = (torch.randn((min(rows, S - s0), N, 2), generator=g, device=dev) * 0.25).clamp_(-1, 1)
+        if fmt == F.IN_I16:
+            d_in[s0:s0 + rows] = torch.round(blk * 32767.0).to(torch.int16)
+        elif fmt == F.IN_U8:
+            d_in[s0:s0 + rows] = (torch.round(blk * 127.0) + 128).clamp_(0, 255).to(torch.uint8)
+        else:
+            d_in[s0:s0 + rows] = blk
+        del blk
+    return d_in
+
+
+def check_rows(S):
+    """rows compared with the oracle after the timed region: first/last of the first 32-stream group, first of the
+    second, the middle, the last, plus one row of every eighth group"""
+    rows = {0, min(31, S - 1), min(32, S - 1), S // 2, S - 1}
+    for g in range(0, (S + 31) // 32, 8):
+        rows.add(min(S - 1, 32 * g + (5 * g + 3) % 32))
+    return sorted(rows)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -228,15 +369,20 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--streams", type=int, default=1024, help="total streams (BASELINE config: 1024)")
-    ap.add_argument("--samples", type=int, default=1 << 20)
+    ap.add_argument("--config", default="cfg5", choices=sorted(WORKLOADS), help="BASELINE.json config (cfg5 = the headline workload)")
+    ap.add_argument("--as-worded", action="store_true", help="cfg1..cfg4: the single-stream shape BASELINE.json words (launch bound) "
+                                                              "instead of the batched one")
+    ap.add_argument("--streams", type=int, default=0, help="total streams (default: the workload's)")
+    ap.add_argument("--samples", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the secondary weak-scaling figure")
     ap.add_argument("--profile-every", type=int, default=3, help="bracket the kernels of every n-th timed step with CUDA events")
     ap.add_argument("--flags", type=int, default=0, help="SFE_FLAG_* for the chain (debug)")
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="weak: every GPU runs the full 1024-stream shard (box = N x 1024 streams); "
-                         "strong: the 1024 streams are split over the N GPUs")
+    ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                    help="strong (default, SURVEY.md 8-e): the workload's streams are split over the N GPUs; "
+                         "weak: every GPU runs the full shard (box = N x streams)")
     args = ap.parse_args()
     capture_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -244,10 +390,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    cfg = dict(F.CONFIGS["cfg5"], S=args.streams, N=args.samples)
+    name = args.config
+    fx, S_b, N_b, S_w, N_w, _ = WORKLOADS[name]
+    S_def, N_def = (S_w, N_w) if args.as_worded else (S_b, N_b)
+    cfg = dict(F.CONFIGS[fx], S=args.streams or S_def, N=args.samples or N_def)
 
     if args.impl == "reference":
-        run_reference(args, cfg, rank, world)
+        run_reference(args, name, cfg, rank, world)
         return
 
     import torch
@@ -263,91 +412,136 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = simplefe_b200.lib()
     simplefe_b200._lib.check(lib.sfe_set_device(local_rank), "sfe_set_device")
-
-    N = cfg["N"]
-    # the path shards by stream with no data-path collective.  weak (default): each GPU carries the
-    # full single-GPU shard of cfg["S"] streams; strong: cfg["S"] streams are split over the ranks.
-    from simplefe_b200.shard import shard_range
-    if args.scaling == "weak":
-        S = cfg["S"]
-    else:
-        lo, hi = shard_range(cfg["S"], rank, n_ranks)
-        S = hi - lo
-        assert cfg["S"] % n_ranks == 0, "strong scaling bench expects streams divisible by the GPU count"
-    S_total = S * n_ranks
     dev = torch.device("cuda", local_rank)
-
-    # synthetic int16 IQ, generated on the device (N(0, 0.25^2) clipped, round(x * 32767)); rank-distinct seed
-    g = torch.Generator(device=dev)
-    g.manual_seed(5000 + rank)
-    d_in = torch.empty((S, N, 2), dtype=torch.int16, device=dev)
-    rows = max(1, (256 << 20) // (N * 2 * 4))
-    for s0 in range(0, S, rows):
-        blk = torch.randn((min(rows, S - s0), N, 2), generator=g, device=dev) * 0.25
-        d_in[s0:s0 + rows] = torch.round(blk.clamp_(-1, 1) * 32767.0).to(torch.int16)
-    del blk
-
-    ch = Chain(S, cfg["in_fmt"], cfg["blkconv"], cfg["stage_a"], cfg["stage_b"], flags=args.flags, device=local_rank)
-    cap = ch.max_out(N)
-    d_out = torch.zeros((S, cap, 2), dtype=torch.float32, device=dev)
-    stream = torch.cuda.current_stream()
-
-    def step():   # one pass of the hot path over one batch: the next 2^20 samples of every stream
-        return ch.process_dev(d_in.data_ptr(), N, N, d_out.data_ptr(), cap, stream.cuda_stream)
+    N = cfg["N"]
+    eb = EB[cfg["in_fmt"]]
+    from simplefe_b200.shard import shard_range
 
     def barrier():
         if n_ranks > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident throughput -----------------------------------------------------------------
-    for _ in range(args.warmup):
-        n_out = step()
-    barrier()
-    # every third step is bracketed with events for the roofline; the others run as a caller's would (a bracketed
-    # step costs two event records and keeps the state carry from running beside the main kernel)
-    ch.profile(args.profile_every)
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    launches0 = lib.sfe_kernel_launches()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    w0 = time.time()
-    e0.record(stream)
-    for _ in range(args.steps):
-        n_out = step()
-    e1.record(stream)
-    barrier()
-    w1 = time.time()
-    ms = e0.elapsed_time(e1)
-    launches = lib.sfe_kernel_launches() - launches0
-    ch.profile(False)
-    # K steps of 0.7 ms are shorter than one nvidia-smi period: the same loop keeps running, untimed, until the
-    # sampler has seen at least 0.25 s of this load; the clocks line covers the timed region plus that continuation
-    w2 = w1
-    if rank == 0:
-        while time.time() - w0 < 0.25:
-            for _ in range(20):
-                step()
-            torch.cuda.synchronize()
-        w2 = time.time()
-    clocks = sampler.stop(w0, w2) if rank == 0 else None
-    if clocks is not None:
-        clocks["window"] = f"timed region ({(w1 - w0) * 1e3:.1f} ms) + untimed continuation of the same loop to {(w2 - w0) * 1e3:.0f} ms"
-    barrier()
-    ch.profile(False)
-    prof = ch.profile_read()
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if n_ranks > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = S_total * N * args.steps / (ms_max * 1e-3) / 1e6
+    def max_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if n_ranks > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def measure(S, seed, scaling_label, with_clocks):
+        """device-resident throughput of S streams on this rank: (ms over K steps max over ranks, details)"""
+        d_in = device_rows(torch, cfg, S, N, dev, seed)
+        ch = Chain(S, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), flags=args.flags, device=local_rank)
+        cap = max(ch.max_out(N), 1)
+        d_out = torch.zeros((S, cap, 2), dtype=torch.float32, device=dev)
+        stream = torch.cuda.current_stream()
+        small = S * N * eb <= (256 << 20)       # input does not exceed L2 by a wide margin: flush between timed steps
+
+        def step():   # one pass of the hot path over one batch: the next N samples of every stream
+            return ch.process_dev(d_in.data_ptr(), N, N, d_out.data_ptr(), cap, stream.cuda_stream)
+
+        for _ in range(args.warmup):
+            n_out = step()
+        barrier()
+        # every third step is bracketed with events for the roofline; the others run as a caller's would (a bracketed
+        # step costs two event records and keeps the state carry from running beside the main kernel)
+        ch.profile(args.profile_every)
+        sampler = ClockSampler(local_rank)
+        if rank == 0 and with_clocks:
+            sampler.start()
+        launches0 = lib.sfe_kernel_launches()
+        barrier()
+        w0 = time.time()
+        host_s = 0.0
+        if small:
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+            for a, b in evs:
+                flush.fill_(1)
+                a.record(stream)
+                h0 = time.perf_counter()
+                n_out = step()
+                host_s += time.perf_counter() - h0
+                b.record(stream)
+            barrier()
+            ms = sum(a.elapsed_time(b) for a, b in evs)
+        else:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            h0 = time.perf_counter()
+            for _ in range(args.steps):
+                n_out = step()
+            host_s = time.perf_counter() - h0
+            e1.record(stream)
+            barrier()
+            ms = e0.elapsed_time(e1)
+        w1 = time.time()
+        launches = lib.sfe_kernel_launches() - launches0
+        ch.profile(False)
+        # K short steps can be shorter than one nvidia-smi period: the same loop keeps running, untimed, until the
+        # sampler has seen at least 0.25 s of this load; the clocks line covers the timed region plus that continuation
+        clocks = None
+        if rank == 0 and with_clocks:
+            while time.time() - w0 < 0.25:
+                for _ in range(20):
+                    step()
+                torch.cuda.synchronize()
+            w2 = time.time()
+            clocks = sampler.stop(w0, w2)
+            clocks["window"] = f"timed region ({(w1 - w0) * 1e3:.1f} ms) + untimed continuation of the same loop to {(w2 - w0) * 1e3:.0f} ms"
+        barrier()
+        prof = ch.profile_read()
+        return dict(ms=max_ranks(ms), ch=ch, d_in=d_in, d_out=d_out, cap=cap, n_out=n_out, launches=launches, prof=prof,
+                    clocks=clocks, host_us=host_s / args.steps * 1e6, small=small)
+
+    # ---- the workload: streams split over the ranks (strong), or the full shard everywhere (weak) ---------------
+    if args.scaling == "strong":
+        assert cfg["S"] % n_ranks == 0, "the strong-scaling bench expects a stream count divisible by the GPU count"
+        lo, hi = shard_range(cfg["S"], rank, n_ranks)
+        S = hi - lo
+        S_total = cfg["S"]
+    else:
+        lo, S = rank * cfg["S"], cfg["S"]
+        S_total = S * n_ranks
+    m = measure(S, 5000 + lo, args.scaling, True)
+    ch, d_in, d_out, cap, n_out = m["ch"], m["d_in"], m["d_out"], m["cap"], m["n_out"]
+    value = S_total * N * args.steps / (m["ms"] * 1e-3) / 1e6
+    plan = ch.plan
+    stream = torch.cuda.current_stream()
+
+    def step():
+        return ch.process_dev(d_in.data_ptr(), N, N, d_out.data_ptr(), cap, stream.cuda_stream)
+
+    # ---- parity of what was just timed: a sample of this rank's rows against the reference's CPU code ---------------
+    parity = None
+    if not args.no_parity:
+        from oracle import oracle as O
+        olib = O.load("auto")
+        rows = check_rows(S)
+        ch.reset()
+        n_d = step()
+        torch.cuda.synchronize()
+        idx = torch.tensor(rows, device=dev)
+        got = d_out.index_select(0, idx)[:, :n_d].cpu().numpy().view(np.complex64)[..., 0]
+        x = d_in.index_select(0, idx).cpu().numpy()
+        ref, _ = O.chain_run(x, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=olib,
+                             n_threads=max(1, min(len(rows), host_threads() // max(n_ranks, 1))))
+        same_shape = got.shape == ref.shape
+        nr = pk = float("inf")
+        if same_shape:
+            errs = [F.err_metrics(got[k], ref[k]) for k in range(len(rows))] if got.shape[1] else [(0.0, 0.0)]
+            nr, pk = max(e[0] for e in errs), max(e[1] for e in errs)
+        nr, pk = max_ranks(nr), max_ranks(pk)
+        parity = {"rows": rows, "ranks": n_ranks, "streams_per_rank": S, "outputs_per_stream": int(n_d),
+                  "nrms_max": nr, "peak_max": pk, "tol": {"nrms": F.NRMS_TOL, "peak": F.PEAK_TOL},
+                  "ok": bool(nr <= F.NRMS_TOL and pk <= F.PEAK_TOL), "oracle": olib.sfeo_kind().decode(),
+                  "what": "the timed launch shape (same chain object, same rows, one call from a fresh stream state) vs the reference classes"}
 
     # ---- end to end through the host-buffer C-ABI call --------------------------------------------
     e2e = None
     if not args.no_e2e:
-        h_in = torch.empty((S, N, 2), dtype=torch.int16, pin_memory=True)
+        h_in = torch.empty(d_in.shape, dtype=d_in.dtype, pin_memory=True)
         h_in.copy_(d_in)
         h_out = torch.zeros((S, cap, 2), dtype=torch.float32, pin_memory=True)
         torch.cuda.synchronize()
@@ -363,14 +557,22 @@ def main():
         for _ in range(k_e2e):
             n_h = step_host()
         torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
-        if n_ranks > 1:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dt = float(tt.item())
+        dt = max_ranks(time.perf_counter() - t0)
         e2e = {"value": S_total * N * k_e2e / dt / 1e6, "unit": METRIC,
-               "h2d_bytes_per_step": int(S * N * 4), "d2h_bytes_per_step": int(S * n_h * 8), "steps": k_e2e,
+               "h2d_bytes_per_step": int(S * N * eb), "d2h_bytes_per_step": int(S * n_h * 8), "steps": k_e2e,
                "api": "sfe_chain_process_host (pinned host in/out, 2 CUDA streams, stream groups double-buffered)"}
+        # what the box can do at best: one plain pinned H2D copy of the same bytes per GPU, all GPUs at once
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            d_in.copy_(h_in, non_blocking=True)
+        torch.cuda.synchronize()
+        dtc = max_ranks(time.perf_counter() - t0)
+        ceil_gbs = 3 * S * N * eb * n_ranks / dtc / 1e9
+        e2e["h2d_ceiling_gbs"] = ceil_gbs
+        e2e["h2d_ceiling_what"] = f"{n_ranks} concurrent cudaMemcpyAsync H2D of {S * N * eb >> 20} MiB each from pinned memory, aggregate"
+        e2e["h2d_achieved_gbs"] = e2e["value"] * 1e6 * eb / 1e9
+        e2e["frac_of_h2d_ceiling"] = e2e["h2d_achieved_gbs"] / ceil_gbs
         # the device-resident and the host path must agree bit for bit from the same stream state
         ch.reset()
         n_d = step()
@@ -379,6 +581,24 @@ def main():
         ch.reset()
         n_h2 = step_host()
         e2e["matches_device_path"] = bool(n_d == n_h2 and torch.equal(h_out[:, :n_h2], ref_dev))
+        del h_in, h_out
+
+    # ---- secondary figure at N > 1: the other scaling mode, device resident only ---------------------------------
+    other = None
+    if n_ranks > 1 and not args.no_weak:
+        del d_in, d_out, ch
+        m["ch"] = m["d_in"] = m["d_out"] = None
+        torch.cuda.empty_cache()
+        if args.scaling == "strong":
+            mo = measure(cfg["S"], 7000 + rank * cfg["S"], "weak", False)
+            tot = cfg["S"] * n_ranks
+        else:
+            lo2, hi2 = shard_range(cfg["S"], rank, n_ranks)
+            mo = measure(hi2 - lo2, 7000 + lo2, "strong", False)
+            tot = cfg["S"]
+        other = {"scaling": "weak" if args.scaling == "strong" else "strong", "value": tot * N * args.steps / (mo["ms"] * 1e-3) / 1e6,
+                 "unit": METRIC, "streams_total": tot, "ms_per_step": mo["ms"] / args.steps}
+        mo["ch"] = mo["d_in"] = mo["d_out"] = None
 
     if rank != 0:
         if n_ranks > 1:
@@ -388,32 +608,39 @@ def main():
 
     # ---- roofline of the dominant kernel ------------------------------------------------------------
     peak, peak_src = measured_peaks()
+    prof = m["prof"]
     dom = max(prof, key=lambda p: p[1]) if prof else ("", 0.0, 0)
-    per_launch_samples = S * N
-    ach = BYTES_ALG_PER_SAMPLE * per_launch_samples / (dom[1] * 1e-3) / 1e9 if dom[1] > 0 else None
-    tr = ncu_traffic()
+    bps = bytes_alg_per_sample(name, cfg, N, n_out)
+    ach = bps * S * N / (dom[1] * 1e-3) / 1e9 if dom[1] > 0 else None
+    # the capture is per launch of the full single-GPU workload; other shard sizes have no capture
+    tr = ncu_traffic(name, plan) if args.flags == 0 and S == WORKLOADS[name][1] and N == WORKLOADS[name][2] and not args.as_worded else None
     roofline = {"bound": "hbm", "kernel": dom[0], "kernel_ms": dom[1], "launches_timed": dom[2], "timed_every": args.profile_every,
                 "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None,
-                "traffic": (tr or {}).get("dram_bytes_per_launch"), "peak_source": peak_src,
-                "bytes_alg_per_sample": BYTES_ALG_PER_SAMPLE,
-                "kernels": [{"name": n, "ms": m, "launches": k} for n, m, k in prof],
-                "whole_step_frac": BYTES_ALG_PER_SAMPLE * value * 1e6 / n_ranks / 1e9 / peak}
+                "traffic": (tr or {}).get("dram_bytes_per_launch"), "traffic_source": (tr or {}).get("source"),
+                "peak_source": peak_src, "bytes_alg_per_sample": bps,
+                "note": "achieved = bytes_alg_per_sample x the samples one launch of this kernel covers / its mean launch duration "
+                        "(a multi-kernel plan's later stages read intermediates: see whole_step_frac)",
+                "kernels": [{"name": n, "ms": ms_, "launches": k} for n, ms_, k in prof],
+                "whole_step_frac": bps * value * 1e6 / n_ranks / 1e9 / peak}
 
     # ---- CPU baseline: the reference's own code on this box's cores ------------------------------
     cpu = None
     if not args.no_cpu and n_ranks == 1:
         try:
-            src = d_in[: min(S, 1024)].cpu().numpy()
-            cpu = cpu_baseline(cfg, lambda k: src[np.arange(k) % len(src)])
+            cpu = cpu_baseline(cfg, host_rows(cfg))
         except Exception as ex:  # the baseline is a report, not a dependency of the GPU numbers
             cpu = {"value": None, "error": repr(ex)}
 
     line = {
         "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": n_ranks, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": dict(workload_config(cfg, n_ranks, S, args.scaling), plan=ch.plan, outputs_per_stream=n_out),
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        "ms_per_step": m["ms"] / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(name, cfg, n_ranks, args.scaling),
+        "plan": plan, "outputs_per_stream": int(n_out),
+        "clocks": m["clocks"], "e2e": e2e, "gpu_launches": int(m["launches"]), "roofline": roofline, "parity": parity,
+        "host_enqueue_us_per_step": m["host_us"], "cpu_baseline": cpu,
     }
+    if other is not None:
+        line[other["scaling"]] = other
     emit(line)
     if n_ranks > 1:
         dist.barrier()

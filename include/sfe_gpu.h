@@ -32,7 +32,8 @@ extern "C" {
 #define SFE_ERR_ARG (-1)      /* bad argument (message in sfe_last_error) */
 #define SFE_ERR_CUDA (-2)     /* CUDA runtime/driver failure: fatal, never papered over */
 #define SFE_ERR_NODEV (-3)    /* no CUDA device / not sm_100 */
-#define SFE_ERR_CAP (-4)      /* caller-provided capacity too small */
+#define SFE_ERR_CAP (-4)      /* caller-provided capacity too small; the stream state is unchanged */
+#define SFE_ERR_HOST (-5)     /* host-side failure (e.g. out of memory); no C++ exception ever crosses this ABI */
 
 /* ---- library ---------------------------------------------------------------------------- */
 const char *sfe_version(void);
@@ -52,8 +53,11 @@ int sfe_stream_sync(void *stream);         /* NULL = the library's default strea
 
 /* ---- (1a) blkconv: libdsp/blkconv.h:35-48, blkconv.cxx:34-122 ------------------------------ */
 typedef struct sfe_blkconv sfe_blkconv;
-/* blkconv::blkconv(float *taps, int n_taps, int fft_len)  blkconv.h:38.  Taps are copied.
-   fft_len must be a power of two in [32, 8192] and n_taps <= fft_len (else NULL + error). */
+/* blkconv::blkconv(float *taps, int n_taps, int fft_len)  blkconv.h:38.  Taps are copied.  Any fft_len >= n_taps
+   works, as in the reference (which hands it to FFTW, blkconv.cxx:60,72-73): the block size is fft_len+1-n_taps and
+   the stream is the causal convolution whatever fft_len is, so the kernels run overlap-save with an internal
+   power-of-two transform (fft_len itself when it is a power of two in [32, 8192]); taps longer than 4097 run as a
+   direct FIR.  NULL + error only for bad arguments or without a CUDA device. */
 sfe_blkconv *sfe_blkconv_create(const float *taps, int n_taps, int fft_len);
 int sfe_blkconv_blksize(sfe_blkconv *h);   /* blkconv::get_blksize  blkconv.h:40 = fft_len+1-n_taps */
 float *sfe_blkconv_buf(sfe_blkconv *h);    /* blkconv::get_process_buf blkconv.h:44: pinned host

@@ -62,12 +62,27 @@ static const float2 *twiddles(int dev, int N)
     }
     float2 *d = nullptr;
     if (!SFE_CUDA(cudaMalloc(&d, sizeof(float2) * h.size()))) return nullptr;
-    if (!SFE_CUDA(cudaMemcpy(d, h.data(), sizeof(float2) * h.size(), cudaMemcpyHostToDevice))) return nullptr;
+    // pageable source: the copy may return before the DMA has landed, and the kernels that read the table run on
+    // non-blocking streams -- wait for the device once, here (one-off per (device, N))
+    if (!SFE_CUDA(cudaMemcpy(d, h.data(), sizeof(float2) * h.size(), cudaMemcpyHostToDevice)) || !SFE_CUDA(cudaDeviceSynchronize()))
+        return nullptr;
     g_tw[{dev, N}] = d;
     return d;
 }
 
 static bool valid_fft(int n) { return n >= 32 && n <= 8192 && (n & (n - 1)) == 0; }
+
+// The FFT size the kernels run for a blkconv(taps, n_taps, fft_len).  The reference hands ANY fft_len to FFTW
+// (blkconv.cxx:60,72-73) and its result -- the causal convolution, emitted in blocks of fft_len+1-n_taps -- does not
+// depend on it, so the size of the internal overlap-save transform is free: a power of two the radix-16
+// kernel is compiled for.  0 = taps too long for any compiled size: the convolution then runs as a direct FIR.
+int blkconv_internal_fft(int n_taps, int fft_len)
+{
+    if (valid_fft(fft_len) && n_taps <= fft_len) return fft_len;
+    for (int n = 32; n <= 8192; n *= 2)
+        if (n >= 4 * n_taps) return n;          // at least 3/4 of every transform is new samples
+    return n_taps <= 4097 ? 8192 : 0;           // at least half
+}
 
 // tap spectrum in kernel order, computed by the forward half of the convolution kernel itself
 static float2 *make_spectrum(int dev, const float *taps, int n_taps, int N, cudaStream_t st)
@@ -102,6 +117,7 @@ static float2 *make_spectrum(int dev, const float *taps, int n_taps, int N, cuda
 }
 
 // entry points for chain.cu
+int chain_blkconv_fft(int n_taps, int fft_len) { return blkconv_internal_fft(n_taps, fft_len); }
 const float2 *chain_twiddles(int dev, int N) { return twiddles(dev, N); }
 float2 *chain_spectrum(int dev, const float *taps, int n_taps, int N, cudaStream_t st)
 {
@@ -176,7 +192,8 @@ extern "C" int sfe_stream_sync(void *st)
 // (1a) blkconv object -- libdsp/blkconv.h:35-48
 // =================================================================================================
 struct sfe_blkconv {
-    int dev, N, n_taps, blk, ov;
+    int dev, N, n_taps, blk, ov;    // N: internal transform size (0 = direct FIR), blk: fft_len + 1 - n_taps
+    float *d_taps = nullptr;        // direct FIR only
     float *h_buf = nullptr;       // pinned, N+2 floats (blkconv.cxx:44)
     float *d_in = nullptr, *d_out = nullptr;
     float *d_hist[2] = {nullptr, nullptr};
@@ -186,16 +203,16 @@ struct sfe_blkconv {
     cudaStream_t st = nullptr;
 };
 
-extern "C" sfe_blkconv *sfe_blkconv_create(const float *taps, int n_taps, int fft_len)
+static sfe_blkconv * sfe_blkconv_create_impl(const float *taps, int n_taps, int fft_len)
 {
-    if (!taps || n_taps < 1 || !valid_fft(fft_len) || n_taps > fft_len) {
-        set_error("blkconv: need taps, 1 <= n_taps <= fft_len, fft_len a power of two in [32, 8192]");
+    if (!taps || n_taps < 1 || n_taps > fft_len || fft_len > (1 << 28)) {
+        set_error("blkconv: need taps and 1 <= n_taps <= fft_len <= 2^28");
         return nullptr;
     }
     if (!device_ready()) return nullptr;
     sfe_blkconv *b = new sfe_blkconv;
     b->dev = g_device;
-    b->N = fft_len;
+    b->N = blkconv_internal_fft(n_taps, fft_len);
     b->n_taps = n_taps;
     b->blk = fft_len + 1 - n_taps;   // blkconv.cxx:47
     b->ov = n_taps - 1;              // blkconv.cxx:48
@@ -209,15 +226,26 @@ extern "C" sfe_blkconv *sfe_blkconv_create(const float *taps, int n_taps, int ff
               SFE_CUDA(cudaMemsetAsync(b->d_hist[1], 0, sizeof(float) * (b->ov + 1), b->st));
     if (ok) {
         memset(b->h_buf, 0, sizeof(float) * (fft_len + 2));
-        b->d_tw = twiddles(b->dev, fft_len);
-        b->d_hp = make_spectrum(b->dev, taps, n_taps, fft_len, b->st);
-        ok = b->d_tw && b->d_hp;
+        if (b->N) {
+            b->d_tw = twiddles(b->dev, b->N);
+            b->d_hp = make_spectrum(b->dev, taps, n_taps, b->N, b->st);
+            ok = b->d_tw && b->d_hp;
+        } else {
+            ok = SFE_CUDA(cudaMalloc(&b->d_taps, sizeof(float) * n_taps)) &&
+                 SFE_CUDA(cudaMemcpyAsync(b->d_taps, taps, sizeof(float) * n_taps, cudaMemcpyHostToDevice, b->st)) &&
+                 SFE_CUDA(cudaStreamSynchronize(b->st));
+        }
     }
     if (!ok) {
         sfe_blkconv_destroy(b);
         return nullptr;
     }
     return b;
+}
+
+extern "C" sfe_blkconv * sfe_blkconv_create(const float *taps, int n_taps, int fft_len)
+{
+    SFE_GUARDED(nullptr, return sfe_blkconv_create_impl(taps, n_taps, fft_len);)
 }
 
 extern "C" int sfe_blkconv_blksize(sfe_blkconv *b) { return b ? b->blk : 0; }
@@ -229,19 +257,40 @@ extern "C" int sfe_blkconv_process(sfe_blkconv *b)
     if (!SFE_CUDA(cudaSetDevice(b->dev))) return SFE_ERR_CUDA;
     if (!SFE_CUDA(cudaMemcpyAsync(b->d_in, b->h_buf, sizeof(float) * b->blk, cudaMemcpyHostToDevice, b->st)))
         return SFE_ERR_CUDA;
-    BlkconvParams p{};
-    p.in = StreamView{b->d_in, b->d_hist[b->cur], b->blk, b->ov, b->blk, SFE_IN_F32};
-    p.in_real = 1;
-    p.out = b->d_out;
-    p.out_pitch = b->blk;
-    p.n_streams = 1;
-    p.n_blocks = 1;
-    p.hop = b->blk;
-    p.ov = b->ov;
-    p.tw = b->d_tw;
-    p.hp = b->d_hp;
-    p.mode = BLKCONV_MODE_CONV;
-    int rc = launch_blkconv(b->N, p, b->st);
+    int rc;
+    if (b->N) {
+        // overlap-save with the internal transform: ceil(blk / hop) FFT blocks cover the call's blk samples
+        BlkconvParams p{};
+        p.in = StreamView{b->d_in, b->d_hist[b->cur], b->blk, b->ov, b->blk, SFE_IN_F32};
+        p.in_real = 1;
+        p.out = b->d_out;
+        p.out_pitch = b->blk;
+        p.n_streams = 1;
+        p.hop = b->N - b->ov;
+        p.n_blocks = (b->blk + p.hop - 1) / p.hop;
+        p.ov = b->ov;
+        p.tw = b->d_tw;
+        p.hp = b->d_hp;
+        p.mode = BLKCONV_MODE_CONV;
+        rc = launch_blkconv(b->N, p, b->st);
+    } else {
+        // taps longer than any compiled transform: y[n] = sum_j h[j] x[n-j] as a one-phase polyphase stage with step 1
+        PolyParams p{};
+        p.in = StreamView{b->d_in, b->d_hist[b->cur], b->blk, b->ov, b->blk, SFE_IN_F32};
+        p.in_real = 1;
+        p.out = b->d_out;
+        p.out_pitch = b->blk;
+        p.n_streams = 1;
+        p.n_out = b->blk;
+        p.taps = b->d_taps;
+        p.n_taps = b->n_taps;
+        p.up = 1;
+        p.uniform = 1;
+        p.pos0 = 0;
+        p.step = 1;
+        p.rate = 1.f;
+        rc = launch_poly_generic(p, b->st);
+    }
     if (rc != SFE_OK) return rc;
     rc = launch_save_tail(b->d_hist[b->cur ^ 1], b->d_hist[b->cur], b->d_in, b->blk, b->blk, b->ov, 4, 1, b->st);
     if (rc != SFE_OK) return rc;
@@ -262,6 +311,7 @@ extern "C" void sfe_blkconv_destroy(sfe_blkconv *b)
     cudaFree(b->d_hist[0]);
     cudaFree(b->d_hist[1]);
     cudaFree(b->d_hp);
+    cudaFree(b->d_taps);
     if (b->st) cudaStreamDestroy(b->st);
     delete b;
 }
@@ -332,7 +382,7 @@ extern "C" int sfe_polyphase_set_exact(sfe_polyphase *h, int exact)
     return SFE_OK;
 }
 
-extern "C" int sfe_polyphase_process(sfe_polyphase *h, const float *in, int n_in, float *out, int out_len, float rate)
+static int sfe_polyphase_process_impl(sfe_polyphase *h, const float *in, int n_in, float *out, int out_len, float rate)
 {
     if (!h || !in || !out) return SFE_ERR_ARG;
     // the reference's argument checks, messages and return value
@@ -345,6 +395,10 @@ extern "C" int sfe_polyphase_process(sfe_polyphase *h, const float *in, int n_in
     }
     if (out_len < floorf(n_in * 1.0f / rate)) { printf("output buffer is not large enough"); return 0; } // decimate.cxx:84-87
     if (n_in <= 0) return 0;
+    if ((double)n_in * h->up + (double)rate * h->up + h->up >= 2147483648.0) {   // 32-bit grid positions (SchedEntry.pos)
+        set_error("decimate/resample: n_in * upsample reaches 2^31; feed the stream in smaller calls");
+        return SFE_ERR_ARG;
+    }
     if (!SFE_CUDA(cudaSetDevice(h->dev))) return SFE_ERR_CUDA;
 
     h->sched.clear();
@@ -386,6 +440,11 @@ extern "C" int sfe_polyphase_process(sfe_polyphase *h, const float *in, int n_in
     h->cur ^= 1;
     if (!SFE_CUDA(cudaStreamSynchronize(h->st))) return SFE_ERR_CUDA;
     return n_out;
+}
+
+extern "C" int sfe_polyphase_process(sfe_polyphase *h, const float *in, int n_in, float *out, int out_len, float rate)
+{
+    SFE_GUARDED(SFE_ERR_HOST, return sfe_polyphase_process_impl(h, in, n_in, out, out_len, rate);)
 }
 
 extern "C" void sfe_polyphase_destroy(sfe_polyphase *h)

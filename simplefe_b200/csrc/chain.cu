@@ -26,6 +26,7 @@ namespace sfe {
 const float2 *chain_twiddles(int dev, int N);
 float2 *chain_spectrum(int dev, const float *taps, int n_taps, int N, cudaStream_t st);
 bool chain_device_ready(int *dev);
+int chain_blkconv_fft(int n_taps, int fft_len);
 }  // namespace sfe
 
 using namespace sfe;
@@ -73,6 +74,7 @@ struct Op {
     int row_len = 0, n_rows = 0, rows_per_phase = 1, nc = 0, n_live = 1;
     long n_first = 0;
     bool bad_sched = false;
+    bool direct_fir = false;       // OP_POLY standing in for blkconv: every sample is an output (pos = k, mu = 0)
     // per call
     long n_in = 0, n_out = 0;
     std::string name;
@@ -122,6 +124,9 @@ std::vector<float> padded_taps(const sfe_stage_desc &s)
     return t;
 }
 
+// Filter tables are uploaded at create time only.  A cudaMemcpy from pageable memory may return once the data is
+// staged, before the DMA has landed, and the chain's streams are non-blocking (they do not order against the legacy
+// stream): sfe_chain_create ends with one cudaDeviceSynchronize that covers every upload made through here.
 bool upload(float **d, const std::vector<float> &h)
 {
     return SFE_CUDA(cudaMalloc(d, sizeof(float) * h.size())) &&
@@ -152,6 +157,25 @@ bool make_toep(Op &op, const std::vector<double> &g)
            SFE_CUDA(cudaMemcpy(op.d_bmat, op.toep.bmat.data(), op.toep.bmat.size(), cudaMemcpyHostToDevice));
 }
 
+// K3 bank tables for every chunk alignment a call can present (n_first mod spc), or the one table that holds all
+// alignments as rows: built and uploaded once, so that no process call ever copies from pageable memory.
+bool make_bank_tables(Op &op)
+{
+    const int spc = 16 / fmt_bytes(op.in_fmt);
+    // the sample scale of the format (SURVEY.md D2 / source_c_impl.cc:126) lives in the taps
+    const double scale = op.in_fmt == SFE_IN_U8 ? (double)(1.0f / 127.0f) : (double)(1.0f / 32767.0f);
+    const int k0 = op.rows_per_phase > 1 ? -1 : 0, k1 = op.rows_per_phase > 1 ? -1 : spc - 1;
+    for (int key = k0; key <= k1; key++) {
+        std::vector<float> rows;
+        int rl = 0, nr = 0, tc = 0;
+        bank_table(op.g, op.D, op.r, op.up, scale, key, spc, rows, &rl, &nr, &tc);
+        float *d = nullptr;
+        if (!upload(&d, rows)) return false;
+        op.d_tables.emplace(key, d);
+    }
+    return true;
+}
+
 bool alloc_hist(Op &op, int S)
 {
     const size_t bytes = (size_t)S * op.H * fmt_bytes(op.in_fmt);
@@ -165,7 +189,7 @@ bool alloc_hist(Op &op, int S)
 
 long stage_max_out(const Op &op, long n)
 {
-    if (op.kind == OP_BLKCONV) return n;
+    if (op.kind == OP_BLKCONV || op.direct_fir) return n;
     if (op.kind == OP_BANK) {
         if (op.has_pre) {
             const long calls = (n + op.pre_blk - 1) / op.pre_blk;
@@ -214,6 +238,12 @@ void plan_call(sfe_chain *c, long n_in)
             walk_batch(op.ws, op.up, op.blk, op.rate, na, op.sched, false);
             op.n_out = (long)op.sched.count;
             if (op.n_out > 0 && !op.sched.uniform) op.bad_sched = true;
+        } else if (op.direct_fir) {
+            op.n_out = n;
+            op.sched.uniform = true;
+            op.sched.pos0 = 0;
+            op.sched.step = 1;
+            op.sched.count = n;
         } else {
             // the closed-form kernels only need the summary; the generic kernel wants every (pos, mu)
             if (op.kind == OP_POLY) {
@@ -234,6 +264,55 @@ void plan_call(sfe_chain *c, long n_in)
         }
         n = op.n_out;
     }
+}
+
+// The schedule state of every stage, saved before plan_call so that a call that fails (capacity, arguments) leaves the
+// stream exactly where it was: the histories are only swapped by a successful call, and the walk states come back
+// from here.
+struct WalkSnap {
+    std::vector<WalkState> ws, pre;
+    long profile_calls = 0;
+};
+WalkSnap snapshot(const sfe_chain *c)
+{
+    WalkSnap s;
+    for (const Op &op : c->ops) {
+        s.ws.push_back(op.ws);
+        s.pre.push_back(op.pre_ws);
+    }
+    s.profile_calls = c->profile_calls;
+    return s;
+}
+void restore(sfe_chain *c, const WalkSnap &s)
+{
+    for (size_t i = 0; i < c->ops.size(); i++) {
+        c->ops[i].ws = s.ws[i];
+        c->ops[i].pre_ws = s.pre[i];
+    }
+    c->profile_calls = s.profile_calls;
+}
+
+// Argument guards that need no state: schedule entries and kernel indices carry 32-bit positions on the L-times grid
+// of one call (SchedEntry.pos), so a call whose grid does not fit is refused instead of wrapping silently.
+int check_call(const sfe_chain *c, long n_in, const char *who)
+{
+    if (n_in > (1L << 30)) {
+        set_error(std::string(who) + ": at most 2^30 samples per stream and call");
+        return SFE_ERR_ARG;
+    }
+    long n = n_in;
+    for (const Op &op : c->ops) {
+        if (op.kind == OP_POLY && !op.direct_fir) {
+            const double grid = (double)n * op.up + (double)op.rate * op.up + op.up;
+            if (grid >= 2147483648.0) {
+                set_error(std::string(who) + ": n_in * upsample of stage '" + op.name + "' reaches 2^31 (" + std::to_string(n) + " * " +
+                          std::to_string(op.up) + "): feed the stream in smaller calls");
+                return SFE_ERR_ARG;
+            }
+        }
+        n = stage_max_out(op, n);
+    }
+    return SFE_OK;
 }
 
 // device part: run all ops for stream rows [s0, s0+ns) on workspace w
@@ -327,15 +406,9 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             const int spc = 16 / eb;                                     // samples per 16-byte chunk
             const int key = op.rows_per_phase > 1 ? -1 : (int)(((op.n_first % spc) + spc) % spc);
             auto it = op.d_tables.find(key);
-            if (it == op.d_tables.end()) {
-                std::vector<float> rows;
-                int rl = 0, nr = 0, tc = 0;
-                // the sample scale of the format (SURVEY.md D2 / source_c_impl.cc:126) lives in the taps
-                const double scale = op.in_fmt == SFE_IN_U8 ? (double)(1.0f / 127.0f) : (double)(1.0f / 32767.0f);
-                bank_table(op.g, op.D, op.r, op.up, scale, key, spc, rows, &rl, &nr, &tc);
-                float *d = nullptr;
-                if (!upload(&d, rows)) return SFE_ERR_CUDA;
-                it = op.d_tables.emplace(key, d).first;
+            if (it == op.d_tables.end()) {   // every key is built by sfe_chain_create (make_bank_tables)
+                set_error("fused bank: no table for alignment key " + std::to_string(key));
+                return SFE_ERR_ARG;
             }
             BankParams p{};
             p.in = in;
@@ -440,7 +513,7 @@ int upload_schedules(sfe_chain *c, cudaStream_t st)
 
 }  // namespace
 
-extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
+static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
 {
     if (!d || d->n_streams < 1 || d->in_fmt < SFE_IN_I16 || d->in_fmt > SFE_IN_F32) {
         set_error("chain: bad descriptor (n_streams >= 1, in_fmt in {I16,U8,F32})");
@@ -455,9 +528,8 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
         set_error("chain: stage b without stage a");
         return nullptr;
     }
-    if (has_bc && (!d->bc_taps || d->bc_ntaps > d->bc_fft || d->bc_fft < 32 || d->bc_fft > 8192 ||
-                   (d->bc_fft & (d->bc_fft - 1)))) {
-        set_error("chain: blkconv needs 1 <= n_taps <= fft_len, fft_len a power of two in [32, 8192]");
+    if (has_bc && (!d->bc_taps || d->bc_ntaps > d->bc_fft || d->bc_fft > (1 << 28))) {
+        set_error("chain: blkconv needs taps and 1 <= n_taps <= fft_len <= 2^28");
         return nullptr;
     }
     for (const sfe_stage_desc *s : {&d->a, &d->b}) {
@@ -542,18 +614,33 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
     const bool staged = !bank;
 
     if (staged && has_bc && !fuse) {
+        // The reference's block size fft_len+1-n_taps (blkconv.cxx:47) only shapes its own calls; the stream it emits
+        // is the causal convolution whatever fft_len is, so the kernels run overlap-save with an internal power-of-two
+        // transform (the caller's fft_len when it is one the radix-16 kernel is compiled for).
         Op op{};
-        op.kind = OP_BLKCONV;
         op.in_fmt = fmt;
-        op.N = d->bc_fft;
         op.bc_ntaps = d->bc_ntaps;
-        op.hop = d->bc_fft + 1 - d->bc_ntaps;  // blkconv.cxx:47
         op.ov = d->bc_ntaps - 1;               // blkconv.cxx:48
-        op.H = op.ov;
-        op.tw = chain_twiddles(dev, op.N);
-        op.hp = chain_spectrum(dev, d->bc_taps, d->bc_ntaps, op.N, nullptr);
-        ok = ok && op.tw && op.hp;
-        op.name = "blkconv_fft" + std::to_string(op.N);
+        op.N = chain_blkconv_fft(d->bc_ntaps, d->bc_fft);
+        if (op.N) {
+            op.kind = OP_BLKCONV;
+            op.hop = op.N - op.ov;
+            op.H = op.ov;
+            op.tw = chain_twiddles(dev, op.N);
+            op.hp = chain_spectrum(dev, d->bc_taps, d->bc_ntaps, op.N, nullptr);
+            ok = ok && op.tw && op.hp;
+            op.name = "blkconv_fft" + std::to_string(op.N);
+        } else {
+            // taps longer than any compiled transform: direct FIR = one-phase polyphase stage with step 1
+            op.kind = OP_POLY;
+            op.direct_fir = true;
+            op.T = d->bc_ntaps;
+            op.up = 1;
+            op.rate = 1.f;
+            op.H = op.T;
+            ok = ok && upload(&op.d_taps, std::vector<float>(d->bc_taps, d->bc_taps + d->bc_ntaps));
+            op.name = "blkconv_direct_fir/T" + std::to_string(op.T);
+        }
         c->ops.push_back(op);
         c->plan += op.name;
         fmt = SFE_IN_F32;
@@ -604,13 +691,20 @@ extern "C" sfe_chain *sfe_chain_create(const sfe_chain_desc *d)
         c->ops.push_back(op);
         fmt = SFE_IN_F32;
     }
-    for (Op &op : c->ops) ok = ok && alloc_hist(op, c->S);
+    for (Op &op : c->ops) ok = ok && alloc_hist(op, c->S) && (op.kind != OP_BANK || make_bank_tables(op));
     for (int i = 0; i < 2 && ok; i++) ok = SFE_CUDA(cudaStreamCreateWithFlags(&c->ws[i].st, cudaStreamNonBlocking));
+    // every table, history fill and spectrum above is on the device before the first process call may read it
+    ok = ok && SFE_CUDA(cudaDeviceSynchronize());
     if (!ok) {
         sfe_chain_destroy(c);
         return nullptr;
     }
     return c;
+}
+
+extern "C" sfe_chain * sfe_chain_create(const sfe_chain_desc *d)
+{
+    SFE_GUARDED(nullptr, return sfe_chain_create_impl(d);)
 }
 
 extern "C" void sfe_chain_destroy(sfe_chain *c)
@@ -697,36 +791,78 @@ extern "C" int sfe_chain_profile_read(sfe_chain *c, int op, float *mean_ms, int 
     return SFE_OK;
 }
 
-extern "C" int sfe_chain_process_dev(sfe_chain *c, const void *d_in, long n_in, long in_pitch, void *d_out,
+static int sfe_chain_process_dev_impl(sfe_chain *c, const void *d_in, long n_in, long in_pitch, void *d_out,
                                      long out_pitch, long *n_out, void *stream)
 {
     if (!c || !d_in || !d_out || n_in < 0 || in_pitch < n_in) {
         set_error("chain_process_dev: bad arguments");
         return SFE_ERR_ARG;
     }
+    int rc = check_call(c, n_in, "chain_process_dev");
+    if (rc != SFE_OK) return rc;
     if (!SFE_CUDA(cudaSetDevice(c->dev))) return SFE_ERR_CUDA;
     static const bool trace = getenv("SFE_TRACE_HOST") != nullptr;   // host time of the three parts of a call, on stderr
     const auto t0 = std::chrono::steady_clock::now();
+    const WalkSnap snap = snapshot(c);
     plan_call(c, n_in);
     const auto t1 = std::chrono::steady_clock::now();
     const long no = c->ops.back().n_out;
     if (n_out) *n_out = no;
     if (out_pitch < no) {
+        restore(c, snap);    // nothing was launched and no history moved: the stream is where it was
         set_error("chain_process_dev: out_pitch smaller than the output count " + std::to_string(no));
-        return SFE_ERR_CAP;  // note: the schedule state has advanced; call sfe_chain_reset
+        return SFE_ERR_CAP;
     }
     cudaStream_t st = (cudaStream_t)stream;
-    int rc = upload_schedules(c, st);
-    if (rc != SFE_OK) return rc;
+    rc = upload_schedules(c, st);
+    if (rc == SFE_OK) rc = run_ops(c, c->ws[0], 0, c->S, d_in, in_pitch, d_out, out_pitch, st);
     const auto t2 = std::chrono::steady_clock::now();
-    rc = run_ops(c, c->ws[0], 0, c->S, d_in, in_pitch, d_out, out_pitch, st);
-    if (rc != SFE_OK) return rc;
+    if (rc != SFE_OK) {
+        restore(c, snap);    // histories are swapped only below; kernels already queued wrote the spare buffers
+        return rc;
+    }
     if (trace) {
-        const auto t3 = std::chrono::steady_clock::now();
         auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
             return std::chrono::duration<double, std::micro>(b - a).count();
         };
-        fprintf(stderr, "sfe host trace: schedule %.0f us, upload %.0f us, launches %.0f us\n", us(t0, t1), us(t1, t2), us(t2, t3));
+        fprintf(stderr, "sfe host trace: schedule %.0f us, upload + launches %.0f us\n", us(t0, t1), us(t1, t2));
+    }
+    c->cur ^= 1;
+    return SFE_OK;
+}
+
+extern "C" int sfe_chain_process_dev(sfe_chain *c, const void *d_in, long n_in, long in_pitch, void *d_out,
+                                     long out_pitch, long *n_out, void *stream)
+{
+    SFE_GUARDED(SFE_ERR_HOST, return sfe_chain_process_dev_impl(c, d_in, n_in, in_pitch, d_out, out_pitch, n_out, stream);)
+}
+
+static int process_host_groups(sfe_chain *c, const void *h_in, long n_in, long in_pitch, void *h_out, long out_pitch, long no);
+
+static int sfe_chain_process_host_impl(sfe_chain *c, const void *h_in, long n_in, long in_pitch, void *h_out,
+                                      long out_pitch, long *n_out)
+{
+    if (!c || !h_in || !h_out || n_in < 0 || in_pitch < n_in) {
+        set_error("chain_process_host: bad arguments");
+        return SFE_ERR_ARG;
+    }
+    int rc = check_call(c, n_in, "chain_process_host");
+    if (rc != SFE_OK) return rc;
+    if (!SFE_CUDA(cudaSetDevice(c->dev))) return SFE_ERR_CUDA;
+    const WalkSnap snap = snapshot(c);
+    plan_call(c, n_in);
+    const long no = c->ops.back().n_out;
+    if (n_out) *n_out = no;
+    if (out_pitch < no) {
+        restore(c, snap);
+        set_error("chain_process_host: out_pitch smaller than the output count " + std::to_string(no));
+        return SFE_ERR_CAP;
+    }
+    rc = process_host_groups(c, h_in, n_in, in_pitch, h_out, out_pitch, no);
+    if (rc != SFE_OK) {
+        restore(c, snap);
+        for (Workspace &w : c->ws) cudaStreamSynchronize(w.st);
+        return rc;
     }
     c->cur ^= 1;
     return SFE_OK;
@@ -735,18 +871,11 @@ extern "C" int sfe_chain_process_dev(sfe_chain *c, const void *d_in, long n_in, 
 extern "C" int sfe_chain_process_host(sfe_chain *c, const void *h_in, long n_in, long in_pitch, void *h_out,
                                       long out_pitch, long *n_out)
 {
-    if (!c || !h_in || !h_out || n_in < 0 || in_pitch < n_in) {
-        set_error("chain_process_host: bad arguments");
-        return SFE_ERR_ARG;
-    }
-    if (!SFE_CUDA(cudaSetDevice(c->dev))) return SFE_ERR_CUDA;
-    plan_call(c, n_in);
-    const long no = c->ops.back().n_out;
-    if (n_out) *n_out = no;
-    if (out_pitch < no) {
-        set_error("chain_process_host: out_pitch smaller than the output count " + std::to_string(no));
-        return SFE_ERR_CAP;
-    }
+    SFE_GUARDED(SFE_ERR_HOST, return sfe_chain_process_host_impl(c, h_in, n_in, in_pitch, h_out, out_pitch, n_out);)
+}
+
+static int process_host_groups(sfe_chain *c, const void *h_in, long n_in, long in_pitch, void *h_out, long out_pitch, long no)
+{
     const int eb = fmt_bytes(c->in_fmt);
     // stream groups of ~64 MiB input: H2D(g+1) overlaps kernels(g) overlaps D2H(g-1) on two CUDA streams
     const size_t row_in = (size_t)n_in * eb;
@@ -780,6 +909,5 @@ extern "C" int sfe_chain_process_host(sfe_chain *c, const void *h_in, long n_in,
     }
     for (Workspace &w : c->ws)
         if (!SFE_CUDA(cudaStreamSynchronize(w.st))) return SFE_ERR_CUDA;
-    c->cur ^= 1;
     return SFE_OK;
 }

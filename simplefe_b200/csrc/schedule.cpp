@@ -22,9 +22,14 @@ int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t 
         st.held = false;
         t = t + step;
     }
-    // the loop writes through a raw pointer into space reserved up front (at most out_len outputs per call)
+    // the loop writes through a raw pointer into space reserved up front: at most out_len outputs per call, and never
+    // more than one per grid position (step >= 1 grid unit), whatever capacity the caller claims to have
     const size_t at = out.size();
-    out.resize(at + (size_t)(out_len > n_out ? out_len - n_out : 0));
+    int64_t room = out_len > n_out ? (int64_t)(out_len - n_out) : 0;
+    const int64_t most = lim + 2 + (st.pos < 0 ? -(int64_t)st.pos : 0);
+    if (room > most) room = most;
+    out_len = n_out + (int)room;                       // the loop below never writes past the reservation
+    out.resize(at + (size_t)room);
     SchedEntry *dst = out.data() + at;
     const int32_t base32 = (int32_t)base;
     // state lives in locals inside the loop (the only loop-carried dependency is t = tf + step); written back after it

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <exception>
 #include <string>
 
 #include "../../include/sfe_gpu.h"
@@ -14,6 +15,17 @@ void set_error(const std::string &msg);
 bool cuda_ok(cudaError_t e, const char *what, const char *file, int line);
 void count_launch(int n = 1);
 #define SFE_CUDA(call) ::sfe::cuda_ok((call), #call, __FILE__, __LINE__)
+// extern "C" entry points that allocate on the host run their body under this guard: no exception crosses the C ABI
+#define SFE_GUARDED(ret_on_throw, ...)                                                        \
+    try {                                                                                     \
+        __VA_ARGS__                                                                           \
+    } catch (const std::exception &e_) {                                                      \
+        ::sfe::set_error(std::string("host-side failure: ") + e_.what());                     \
+        return ret_on_throw;                                                                  \
+    } catch (...) {                                                                           \
+        ::sfe::set_error("host-side failure: unknown exception");                             \
+        return ret_on_throw;                                                                  \
+    }
 
 // ---- complex helpers -------------------------------------------------------------------------
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }

@@ -17,6 +17,12 @@ __global__ void save_tail_kernel(uint16_t *hn, const uint16_t *ho, const uint16_
         const long src = n_u + i - H_u;  // index into cur when >= 0, else into the old history
         hn[(long)s * H_u + i] = src >= 0 ? cur[(long)s * pitch_u + src] : ho[(long)s * H_u + (H_u + src)];
     }
+    // Launched as a programmatic dependent of the main kernel (which executes griddepcontrol.launch_dependents on
+    // entry), this grid runs BESIDE it: the copies above need nothing the main kernel writes.  The wait at the end
+    // keeps the stream order well defined -- this grid completes only after the primary has completed and flushed, so
+    // whatever follows on the stream (a D2H copy of the outputs, the caller's own kernels) sees the main kernel's
+    // results.  Without the launch attribute the instruction is a no-op.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // examples/bpsk/bpsk.cxx:76-101 / gr-simplefe/lib/sink_c_impl.cc:118-144:
