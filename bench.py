@@ -378,7 +378,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the secondary weak-scaling figure")
-    ap.add_argument("--profile-every", type=int, default=3, help="bracket the kernels of every n-th timed step with CUDA events")
+    ap.add_argument("--profile-every", type=int, default=5,
+                    help="bracket the kernels of every n-th timed step with CUDA events (0 = never).  A bracketed step cannot chain "
+                         "its launch behind the previous call's (the event record sits between them), so it is a few us slower")
     ap.add_argument("--flags", type=int, default=0, help="SFE_FLAG_* for the chain (debug)")
     ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
                     help="strong (default, SURVEY.md 8-e): the workload's streams are split over the N GPUs; "
@@ -445,8 +447,8 @@ def main():
         for _ in range(args.warmup):
             n_out = step()
         barrier()
-        # every third step is bracketed with events for the roofline; the others run as a caller's would (a bracketed
-        # step costs two event records and keeps the state carry from running beside the main kernel)
+        # every fifth step is bracketed with events for the roofline; the others run as a caller's would (a bracketed
+        # step costs two event records and cannot start as a programmatic dependent of the previous call's kernel)
         ch.profile(args.profile_every)
         sampler = ClockSampler(local_rank)
         if rank == 0 and with_clocks:
@@ -573,14 +575,20 @@ def main():
         e2e["h2d_ceiling_what"] = f"{n_ranks} concurrent cudaMemcpyAsync H2D of {S * N * eb >> 20} MiB each from pinned memory, aggregate"
         e2e["h2d_achieved_gbs"] = e2e["value"] * 1e6 * eb / 1e9
         e2e["frac_of_h2d_ceiling"] = e2e["h2d_achieved_gbs"] / ceil_gbs
-        # the device-resident and the host path must agree bit for bit from the same stream state
+        # the device-resident and the host path must agree from the same stream state
         ch.reset()
         n_d = step()
         torch.cuda.synchronize()
         ref_dev = d_out.cpu()[:, :n_d].clone()
         ch.reset()
         n_h2 = step_host()
-        e2e["matches_device_path"] = bool(n_d == n_h2 and torch.equal(h_out[:, :n_h2], ref_dev))
+        # (to rounding: the host path launches stream groups, whose work items are cut at other places than the full launch's)
+        if n_d == n_h2 and n_d > 0:
+            dn, dp = F.err_metrics(h_out[:, :n_h2].numpy().view(np.complex64)[..., 0], ref_dev.numpy().view(np.complex64)[..., 0])
+        else:
+            dn, dp = (0.0, 0.0) if n_d == n_h2 else (float("inf"), float("inf"))
+        e2e["matches_device_path"] = bool(n_d == n_h2 and dn <= 1e-6 and dp <= 5e-6)
+        e2e["vs_device_path"] = {"nrms": dn, "peak": dp, "bit_identical": bool(n_d == n_h2 and torch.equal(h_out[:, :n_h2], ref_dev))}
         del h_in, h_out
 
     # ---- secondary figure at N > 1: the other scaling mode, device resident only ---------------------------------
@@ -619,7 +627,9 @@ def main():
                 "traffic": (tr or {}).get("dram_bytes_per_launch"), "traffic_source": (tr or {}).get("source"),
                 "peak_source": peak_src, "bytes_alg_per_sample": bps,
                 "note": "achieved = bytes_alg_per_sample x the samples one launch of this kernel covers / its mean launch duration "
-                        "(a multi-kernel plan's later stages read intermediates: see whole_step_frac)",
+                        "(a multi-kernel plan's later stages read intermediates: see whole_step_frac).  kernel_ms comes from the "
+                        "bracketed steps, whose launch cannot chain behind the previous call's kernel: it includes the launch "
+                        "latency the other steps hide, so it can exceed ms_per_step by a few us",
                 "kernels": [{"name": n, "ms": ms_, "launches": k} for n, ms_, k in prof],
                 "whole_step_frac": bps * value * 1e6 / n_ranks / 1e9 / peak}
 

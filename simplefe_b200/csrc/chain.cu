@@ -341,6 +341,7 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
         char *hist_new = static_cast<char *>(op.hist[c->cur ^ 1]) + (size_t)s0 * op.H * eb;
         StreamView in{src, hist_old, src_pitch, op.H, op.n_in, op.in_fmt};
         int rc = SFE_OK;
+        bool carried = false;                    // the op's kernel wrote the new history itself
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (c->profile && op.ev.size() < 256) {
             if (!SFE_CUDA(cudaEventCreate(&e0)) || !SFE_CUDA(cudaEventCreate(&e1)) || !SFE_CUDA(cudaEventRecord(e0, st)))
@@ -428,7 +429,9 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             p.n_live = op.n_live;
             p.n_rows = op.n_rows;
             p.rows_per_phase = op.rows_per_phase;
+            p.hist_new = hist_new;               // the kernel carries the state itself: one launch per call
             rc = launch_bank(p, st);
+            carried = rc == SFE_OK;
         } else if (op.kind == OP_POLY && op.n_out > 0) {
             PolyParams p{};
             p.in = in;
@@ -453,8 +456,10 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             if (!SFE_CUDA(cudaEventRecord(e1, st))) return SFE_ERR_CUDA;
             op.ev.emplace_back(e0, e1);
         }
-        rc = launch_save_tail(hist_new, hist_old, src, src_pitch, op.n_in, op.H, eb, ns, st, op.kind == OP_BANK && !e0);
-        if (rc != SFE_OK) return rc;
+        if (!carried) {
+            rc = launch_save_tail(hist_new, hist_old, src, src_pitch, op.n_in, op.H, eb, ns, st);
+            if (rc != SFE_OK) return rc;
+        }
         src = dst;
         src_pitch = dst_pitch;
     }

