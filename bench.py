@@ -363,6 +363,135 @@ def check_rows(S):
 
 
 # ---------------------------------------------------------------------------------------------------
+def run_box(args, name, cfg):
+    """--box: the same workload on N GPUs from one process.  The library partitions the streams (sfe_box_create) and
+    drives every GPU from its own worker thread; torch only provides per-device memory, streams and events."""
+    import torch
+    import simplefe_b200
+    from simplefe_b200.chain import Box
+    lib = simplefe_b200.lib()
+    G, N, eb = args.gpus, cfg["N"], EB[cfg["in_fmt"]]
+    assert args.scaling == "strong", "--box runs the split workload"
+    box = Box(cfg["S"], cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), flags=args.flags, n_devices=G)
+    assert box.n_devices == G, (box.n_devices, G)
+    cap = max(box.max_out(N), 1)
+    ranges = [box.stream_range(g) for g in range(G)]
+    d_in, d_out, streams = [], [], []
+    for dev_i, s0, ns in ranges:
+        dev = torch.device("cuda", dev_i)
+        with torch.cuda.device(dev):
+            d_in.append(device_rows(torch, cfg, ns, N, dev, 5000 + s0))
+            d_out.append(torch.zeros((ns, cap, 2), dtype=torch.float32, device=dev))
+            streams.append(torch.cuda.current_stream(dev))
+    pin, pout, pst = [t.data_ptr() for t in d_in], [t.data_ptr() for t in d_out], [s.cuda_stream for s in streams]
+
+    def step():
+        return box.process_dev(pin, N, N, pout, cap, pst)
+
+    def sync_all():
+        for g in range(G):
+            torch.cuda.synchronize(g)
+
+    for _ in range(args.warmup):
+        n_out = step()
+    sync_all()
+    sampler = ClockSampler(0)
+    sampler.start()
+    launches0 = lib.sfe_kernel_launches()
+    ev = []
+    for g in range(G):
+        with torch.cuda.device(g):
+            ev.append((torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)))
+    w0 = time.time()
+    for g in range(G):
+        ev[g][0].record(streams[g])
+    h0 = time.perf_counter()
+    for _ in range(args.steps):
+        n_out = step()
+    host_us = (time.perf_counter() - h0) / args.steps * 1e6
+    for g in range(G):
+        ev[g][1].record(streams[g])
+    sync_all()
+    w1 = time.time()
+    ms = max(a.elapsed_time(b) for a, b in ev)              # device time, max over the GPUs
+    launches = lib.sfe_kernel_launches() - launches0
+    while time.time() - w0 < 0.25:
+        for _ in range(20):
+            step()
+        sync_all()
+    w2 = time.time()
+    clocks = sampler.stop(w0, w2)
+    clocks["window"] = f"timed region ({(w1 - w0) * 1e3:.1f} ms) + untimed continuation of the same loop to {(w2 - w0) * 1e3:.0f} ms (GPU 0)"
+    value = cfg["S"] * N * args.steps / (ms * 1e-3) / 1e6
+
+    parity = None
+    if not args.no_parity:
+        from oracle import oracle as O
+        olib = O.load("auto")
+        box.reset()
+        n_d = step()
+        sync_all()
+        nr = pk = 0.0
+        rows_all = []
+        for g, (dev_i, s0, ns) in enumerate(ranges):
+            rows = check_rows(ns)
+            idx = torch.tensor(rows, device=d_in[g].device)
+            got = d_out[g].index_select(0, idx)[:, :n_d].cpu().numpy().view(np.complex64)[..., 0]
+            x = d_in[g].index_select(0, idx).cpu().numpy()
+            ref, _ = O.chain_run(x, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=olib,
+                                 n_threads=max(1, min(len(rows), host_threads())))
+            if got.shape != ref.shape:
+                nr = pk = float("inf")
+                continue
+            for k in range(len(rows)):
+                a, b = F.err_metrics(got[k], ref[k])
+                nr, pk = max(nr, a), max(pk, b)
+            rows_all.append([s0 + r for r in rows])
+        parity = {"rows": rows_all, "devices": G, "outputs_per_stream": int(n_d), "nrms_max": nr, "peak_max": pk,
+                  "tol": {"nrms": F.NRMS_TOL, "peak": F.PEAK_TOL}, "ok": bool(nr <= F.NRMS_TOL and pk <= F.PEAK_TOL),
+                  "oracle": olib.sfeo_kind().decode()}
+
+    e2e = None
+    if not args.no_e2e:
+        S = cfg["S"]
+        nb_in, nb_out = S * N * eb, S * cap * 8
+        p_in, p_out = lib.sfe_pinned_alloc(nb_in), lib.sfe_pinned_alloc(nb_out)
+        assert p_in and p_out, simplefe_b200.last_error()
+        import ctypes as C
+        h_in = np.ctypeslib.as_array(C.cast(p_in, C.POINTER(C.c_uint8)), shape=(nb_in,))
+        for g, (dev_i, s0, ns) in enumerate(ranges):
+            h_in[s0 * N * eb:(s0 + ns) * N * eb] = d_in[g].cpu().numpy().view(np.uint8).reshape(-1)
+        for _ in range(2):
+            box.process_host_raw(p_in, N, N, p_out, cap)
+        k_e2e = max(2, min(args.steps, 5))
+        t0 = time.perf_counter()
+        for _ in range(k_e2e):
+            n_h = box.process_host_raw(p_in, N, N, p_out, cap)
+        dt = time.perf_counter() - t0
+        e2e = {"value": S * N * k_e2e / dt / 1e6, "unit": METRIC, "h2d_bytes_per_step": int(nb_in), "d2h_bytes_per_step": int(S * n_h * 8),
+               "steps": k_e2e, "api": "sfe_box_process_host (pinned host in/out; per GPU: worker thread, 2 CUDA streams, stream groups double-buffered)"}
+        e2e["h2d_achieved_gbs"] = e2e["value"] * 1e6 * eb / 1e9
+        lib.sfe_pinned_free(p_in)
+        lib.sfe_pinned_free(p_out)
+
+    peak, peak_src = measured_peaks()
+    bps = bytes_alg_per_sample(name, cfg, N, n_out)
+    line = {
+        "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": G, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(name, cfg, G, "strong"),
+        "launcher": "one process: sfe_box_* (library-side stream partition, one host worker thread per GPU)",
+        "plan": box.plan, "outputs_per_stream": int(n_out), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "peak": peak, "unit": "GB/s", "peak_source": peak_src, "bytes_alg_per_sample": bps,
+                     "whole_step_frac": bps * value * 1e6 / G / 1e9 / peak, "achieved": bps * value * 1e6 / G / 1e9,
+                     "frac": bps * value * 1e6 / G / 1e9 / peak, "traffic": None,
+                     "note": "whole step per GPU (no per-kernel brackets in box mode)"},
+        "parity": parity, "host_enqueue_us_per_step": host_us, "cpu_baseline": None,
+    }
+    emit(line)
+
+
+# ---------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -382,6 +511,9 @@ def main():
                     help="bracket the kernels of every n-th timed step with CUDA events (0 = never).  A bracketed step cannot chain "
                          "its launch behind the previous call's (the event record sits between them), so it is a few us slower")
     ap.add_argument("--flags", type=int, default=0, help="SFE_FLAG_* for the chain (debug)")
+    ap.add_argument("--box", action="store_true",
+                    help="N GPUs from ONE process through sfe_box_* (a host worker thread per GPU inside the library) instead of "
+                         "one torchrun rank per GPU; same workload, same keys")
     ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
                     help="strong (default, SURVEY.md 8-e): the workload's streams are split over the N GPUs; "
                          "weak: every GPU runs the full shard (box = N x streams)")
@@ -399,6 +531,10 @@ def main():
 
     if args.impl == "reference":
         run_reference(args, name, cfg, rank, world)
+        return
+
+    if args.box:
+        run_box(args, name, cfg)
         return
 
     import torch

@@ -43,7 +43,7 @@ int sfe_set_device(int device);            /* device used by objects created aft
 int64_t sfe_kernel_launches(void);         /* kernels launched by this library since load */
 
 /* ---- raw memory / stream helpers (for hosts without their own CUDA bindings) -------------- */
-void *sfe_pinned_alloc(size_t bytes);      /* cudaHostAlloc; NULL on failure */
+void *sfe_pinned_alloc(size_t bytes);      /* cudaHostAlloc, pinned for every device of the box; NULL on failure */
 void sfe_pinned_free(void *p);
 void *sfe_dev_alloc(size_t bytes);
 void sfe_dev_free(void *p);
@@ -153,6 +153,31 @@ int sfe_chain_profile_enable(sfe_chain *c, int on);
 /* mean duration in ms of op's main kernel over the calls since enable / the previous read
    (synchronises on the recorded events); *n_samples = launches averaged */
 int sfe_chain_profile_read(sfe_chain *c, int op, float *mean_ms, int *n_samples);
+
+/* ---- (2b) the whole box: the batched chain over every GPU of one node (additive) ---------------------- */
+/* The path shards by stream and by nothing else -- all state is per object (libdsp/blkconv.h:51-61, decimate.h:48-59,
+   resample.h:49-59) -- so device g of G owns the contiguous stream range [g*S/G, (g+1)*S/G) with its own chain, its own
+   host worker thread, and its own pinned-host/device double buffering on two CUDA streams.  No collective, no inter-GPU
+   traffic.  n_devices: how many of the visible devices to use (0 = all; devices 0..n-1).  desc.n_streams is the TOTAL. */
+typedef struct sfe_box sfe_box;
+sfe_box *sfe_box_create(const sfe_chain_desc *desc, int n_devices);
+void sfe_box_destroy(sfe_box *b);
+int sfe_box_n_devices(sfe_box *b);
+/* streams [*first, *first + *count) run on the returned device ordinal; index < sfe_box_n_devices */
+int sfe_box_stream_range(sfe_box *b, int index, int *first, int *count);
+int sfe_box_reset(sfe_box *b);
+long sfe_box_max_out(sfe_box *b, long n_in);
+const char *sfe_box_plan(sfe_box *b);
+/* Host buffers holding ALL S streams (rows as in sfe_chain_process_host; allocate them with sfe_pinned_alloc, which
+   pins for every device): each device's worker runs its stream range through sfe_chain_process_host at the same time.
+   Returns when every device has finished and the whole result is in h_out. */
+int sfe_box_process_host(sfe_box *b, const void *h_in, long n_in, long in_pitch, void *h_out, long out_pitch, long *n_out);
+/* Device-resident: d_in[g] / d_out[g] are the row blocks of device ordinal g's stream range, resident on that device;
+   streams[g] the cudaStream_t to enqueue on (streams == NULL: each device's default stream).  Enqueues on every
+   device and returns without synchronising (sfe_box_sync waits for all devices). */
+int sfe_box_process_dev(sfe_box *b, const void *const *d_in, long n_in, long in_pitch, void *const *d_out, long out_pitch,
+                        long *n_out, void *const *streams);
+int sfe_box_sync(sfe_box *b);
 
 /* ---- (3) ring_buffer<T>: libdsp/ringbuf.h:37-142 (same body in gr-simplefe/lib/ringbuf.h:40-145) ------ */
 /* Byte-oriented twin of the reference template; include/libdsp/ringbuf.h forwards ring_buffer<T> to

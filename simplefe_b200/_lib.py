@@ -62,6 +62,16 @@ SYMBOLS = {
     "sfe_chain_op_name": (C.c_char_p, [_vp, _ci]),
     "sfe_chain_profile_enable": (_ci, [_vp, _ci]),
     "sfe_chain_profile_read": (_ci, [_vp, _ci, C.POINTER(C.c_float), C.POINTER(_ci)]),
+    "sfe_box_create": (_vp, [C.POINTER(ChainDesc), _ci]),
+    "sfe_box_destroy": (None, [_vp]),
+    "sfe_box_n_devices": (_ci, [_vp]),
+    "sfe_box_stream_range": (_ci, [_vp, _ci, C.POINTER(_ci), C.POINTER(_ci)]),
+    "sfe_box_reset": (_ci, [_vp]),
+    "sfe_box_max_out": (_cl, [_vp, _cl]),
+    "sfe_box_plan": (C.c_char_p, [_vp]),
+    "sfe_box_process_host": (_ci, [_vp, _vp, _cl, _cl, _vp, _cl, C.POINTER(_cl)]),
+    "sfe_box_process_dev": (_ci, [_vp, C.POINTER(_vp), _cl, _cl, C.POINTER(_vp), _cl, C.POINTER(_cl), C.POINTER(_vp)]),
+    "sfe_box_sync": (_ci, [_vp]),
     "sfe_pack_dac10_dev": (_ci, [_vp, _cl, _vp, _vp]),
     "sfe_bpsk_tx_create": (_vp, [_f32p, _ci, _ci, _cf, _ci]),
     "sfe_bpsk_tx_destroy": (None, [_vp]),

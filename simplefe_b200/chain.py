@@ -132,3 +132,70 @@ class Chain:
         h, self._h = getattr(self, "_h", None), None
         if h:
             self._l.sfe_chain_destroy(h)
+
+
+class Box:
+    """The batched chain over the GPUs of one box (sfe_box_* in include/sfe_gpu.h): contiguous stream ranges per
+    device, one worker thread and one double-buffered copy pipeline per device, no collective."""
+
+    def __init__(self, n_streams: int, in_fmt: int = IN_I16, blkconv=None, stage_a=None, stage_b=None, flags: int = 0,
+                 n_devices: int = 0):
+        self._l = lib()
+        d, keep = make_desc(n_streams, in_fmt, blkconv, stage_a, stage_b, flags)
+        self._h = self._l.sfe_box_create(C.byref(d), int(n_devices))
+        if not self._h:
+            raise SfeError(f"sfe_box_create: {last_error()}")
+        self.n_streams, self.in_fmt = int(n_streams), int(in_fmt)
+        self.n_devices = int(self._l.sfe_box_n_devices(self._h))
+
+    @property
+    def plan(self) -> str:
+        return self._l.sfe_box_plan(self._h).decode()
+
+    def stream_range(self, index: int):
+        """(device ordinal, first stream, stream count) of shard `index`"""
+        a, n = C.c_int(0), C.c_int(0)
+        dev = check(self._l.sfe_box_stream_range(self._h, int(index), C.byref(a), C.byref(n)), "sfe_box_stream_range")
+        return dev, int(a.value), int(n.value)
+
+    def reset(self):
+        check(self._l.sfe_box_reset(self._h), "sfe_box_reset")
+
+    def sync(self):
+        check(self._l.sfe_box_sync(self._h), "sfe_box_sync")
+
+    def max_out(self, n_in: int) -> int:
+        return int(self._l.sfe_box_max_out(self._h, int(n_in)))
+
+    def process_host_raw(self, h_in: int, n_in: int, in_pitch: int, h_out: int, out_pitch: int) -> int:
+        n_out = C.c_long(0)
+        check(self._l.sfe_box_process_host(self._h, h_in, int(n_in), int(in_pitch), h_out, int(out_pitch), C.byref(n_out)),
+              "sfe_box_process_host")
+        return int(n_out.value)
+
+    def process_dev(self, d_in, n_in: int, in_pitch: int, d_out, out_pitch: int, streams=None) -> int:
+        """d_in / d_out / streams: one raw pointer (int) per device ordinal"""
+        G = self.n_devices
+        a = (C.c_void_p * G)(*[int(x) for x in d_in])
+        o = (C.c_void_p * G)(*[int(x) for x in d_out])
+        st = (C.c_void_p * G)(*[int(x) for x in streams]) if streams is not None else None
+        n_out = C.c_long(0)
+        check(self._l.sfe_box_process_dev(self._h, a, int(n_in), int(in_pitch), o, int(out_pitch), C.byref(n_out), st),
+              "sfe_box_process_dev")
+        return int(n_out.value)
+
+    def process(self, iq: np.ndarray) -> np.ndarray:
+        """iq: (S, N, 2) host array in the box's input format -> complex64 (S, n_out)."""
+        iq = np.ascontiguousarray(iq, dtype=_NP_DT[self.in_fmt])
+        S, N, two = iq.shape
+        if S != self.n_streams or two != 2:
+            raise ValueError("iq must be (n_streams, N, 2)")
+        cap = max(self.max_out(N), 1)
+        out = np.zeros((S, cap), np.complex64)
+        n = self.process_host_raw(iq.ctypes.data, N, N, out.ctypes.data, cap)
+        return out[:, :n]
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._l.sfe_box_destroy(h)

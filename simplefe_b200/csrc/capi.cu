@@ -163,7 +163,7 @@ extern "C" void *sfe_pinned_alloc(size_t bytes)
 {
     void *p = nullptr;
     if (!device_ready()) return nullptr;
-    if (!SFE_CUDA(cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault))) return nullptr;
+    if (!SFE_CUDA(cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable))) return nullptr;
     return p;
 }
 extern "C" void sfe_pinned_free(void *p) { if (p) cudaFreeHost(p); }

@@ -39,6 +39,10 @@ def test_no_cpu_fallback_without_device():
     from simplefe_b200 import pydsp
     with pytest.raises(_lib.SfeError):
         pydsp.resample([1.0, 2.0], 2, 64)
+    # the multi-device entry point fails the same way: no worker threads, no CPU path
+    from simplefe_b200.chain import Box, stage
+    with pytest.raises(_lib.SfeError, match="no CUDA device|no CPU fallback|cudaGetDeviceCount"):
+        Box(4, 0, None, stage(1, [1.0, 2.0, 1.0], 1, 64, 2.0))
 
 
 def test_product_never_touches_oracle():

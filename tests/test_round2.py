@@ -262,3 +262,67 @@ def test_cfg4_ragged_split_vs_reference_objects(gpu_lib, oracle_lib, S, flags):
     assert whole.shape == ref_whole.shape and whole.shape[1] > 10000
     nrms, peak = F.err_metrics(whole, ref_whole)
     assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
+
+
+# ---- the whole box from one process: sfe_box_* (library-side stream partition, one worker thread per GPU) ---------------
+
+@pytest.mark.parametrize("base,S,N", [("cfg5_small", 70, 70001), ("cfg4_small", 5, 30000), ("cfg2_small", 3, 50003)])
+def test_box_vs_oracle(gpu_lib, oracle_lib, base, S, N):
+    """every visible device (two on the 2-GPU test box, one otherwise): contiguous stream ranges, two ragged calls"""
+    from oracle import oracle as O
+    from simplefe_b200.chain import Box
+    cfg = dict(F.CONFIGS[base], S=S, N=N)
+    iq = F.make_input(cfg)
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=4)
+    n_dev = min(gpu_lib.sfe_device_count(), S)
+    box = Box(S, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), n_devices=0)
+    assert box.n_devices == n_dev
+    covered = []
+    for g in range(box.n_devices):
+        dev, s0, ns = box.stream_range(g)
+        assert dev == g and ns in (S // n_dev, S // n_dev + 1)
+        covered += list(range(s0, s0 + ns))
+    assert covered == list(range(S)), "contiguous ranges [g*S/G, (g+1)*S/G) cover every stream once"
+    if base == "cfg4_small":
+        got = box.process(iq)                      # fractional rates: the reference's stream depends on the call split
+    else:
+        cut = N // 2 + 123
+        got = np.concatenate([box.process(iq[:, :cut]), box.process(iq[:, cut:])], axis=1)
+    assert got.shape == ref.shape, (box.plan, got.shape, ref.shape)
+    for s in range(S):
+        nrms, peak = F.err_metrics(got[s], ref[s])
+        assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (s, box.plan, nrms, peak)
+    box.reset()
+    again = box.process(iq)
+    assert again.shape == ref.shape
+
+
+def test_box_one_device_equals_chain(gpu_lib):
+    from simplefe_b200.chain import Box
+    cfg = dict(F.CONFIGS["cfg5_small"], S=9, N=40000)
+    iq = F.make_input(cfg)
+    one = Box(cfg["S"], cfg["in_fmt"], cfg["blkconv"], cfg["stage_a"], cfg["stage_b"], n_devices=1).process(iq)
+    ref = _chain(cfg).process(iq)
+    assert np.array_equal(one, ref)
+
+
+def test_box_device_resident(gpu_lib, oracle_lib):
+    import torch
+    from oracle import oracle as O
+    from simplefe_b200.chain import Box
+    cfg = dict(F.CONFIGS["cfg5_small"], S=66, N=50001)
+    iq = F.make_input(cfg)
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg["blkconv"], cfg["stage_a"], cfg["stage_b"], lib=oracle_lib, n_threads=4)
+    box = Box(cfg["S"], cfg["in_fmt"], cfg["blkconv"], cfg["stage_a"], cfg["stage_b"])
+    cap = box.max_out(cfg["N"])
+    d_in, d_out = [], []
+    for g in range(box.n_devices):
+        dev, s0, ns = box.stream_range(g)
+        d_in.append(torch.from_numpy(iq[s0:s0 + ns]).to(f"cuda:{dev}"))
+        d_out.append(torch.zeros((ns, cap, 2), dtype=torch.float32, device=f"cuda:{dev}"))
+    n = box.process_dev([t.data_ptr() for t in d_in], cfg["N"], cfg["N"], [t.data_ptr() for t in d_out], cap)
+    box.sync()
+    got = np.concatenate([t.cpu().numpy()[:, :n].view(np.complex64)[..., 0] for t in d_out], axis=0)
+    assert got.shape == ref.shape
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
