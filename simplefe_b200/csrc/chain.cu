@@ -56,6 +56,11 @@ struct Op {
     size_t h_sched_cap = 0;
     cudaEvent_t h_sched_done = nullptr;
     void *reg_ptr = nullptr;         // storage of sched.e while it is registered as pinned memory (copied from in place)
+    // fractional steps: the schedule as closed-form runs, expanded on the device
+    bool use_runs = false;
+    RunVec runs;
+    SchedRun *h_runs = nullptr, *d_runs = nullptr;   // pinned staging copy / device copy
+    size_t h_runs_cap = 0, d_runs_cap = 0;
     // decimating FIR
     int D = 0, QLP = 0;
     float *d_gp = nullptr;
@@ -245,6 +250,16 @@ void plan_call(sfe_chain *c, long n_in)
             op.sched.step = 1;
             op.sched.count = n;
         } else {
+            const float stepf = op.rate * (float)op.up;
+            op.use_runs = op.kind == OP_POLY && stepf != floorf(stepf);
+            if (op.use_runs) {
+                // fractional step: a few closed-form runs per reference call; the device expands them (upload_schedules)
+                op.n_out = (long)walk_batch_runs(op.ws, op.up, op.blk, op.rate, n, op.runs);
+                op.sched.uniform = false;
+                op.sched.count = op.n_out;
+                n = op.n_out;
+                continue;
+            }
             // the closed-form kernels only need the summary; the generic kernel wants every (pos, mu)
             if (op.kind == OP_POLY) {
                 // The entry list is copied to the device from where the walk writes it (its storage is registered as pinned
@@ -480,6 +495,32 @@ int upload_schedules(sfe_chain *c, cudaStream_t st)
             op.d_sched_cap = need * 2;
         }
         if (!op.h_sched_done && !SFE_CUDA(cudaEventCreateWithFlags(&op.h_sched_done, cudaEventDisableTiming))) return SFE_ERR_CUDA;
+        if (op.use_runs) {
+            // run list -> pinned staging -> device, then one small kernel writes the n_out entries where the kernels read them
+            const size_t nr = op.runs.size(), rb = nr * sizeof(SchedRun);
+            if (op.h_runs_cap < rb) {
+                if (op.h_runs) {
+                    cudaEventSynchronize(op.h_sched_done);
+                    cudaFreeHost(op.h_runs);
+                }
+                cudaFree(op.d_runs);
+                op.h_runs = nullptr;
+                op.d_runs = nullptr;
+                op.h_runs_cap = op.d_runs_cap = 0;
+                if (!SFE_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&op.h_runs), rb * 2, cudaHostAllocDefault)) ||
+                    !SFE_CUDA(cudaMalloc(&op.d_runs, rb * 2)))
+                    return SFE_ERR_CUDA;
+                op.h_runs_cap = op.d_runs_cap = rb * 2;
+            }
+            if (!SFE_CUDA(cudaEventSynchronize(op.h_sched_done))) return SFE_ERR_CUDA;   // the previous call's copy has left the staging buffer
+            memcpy(op.h_runs, op.runs.data(), rb);
+            if (!SFE_CUDA(cudaMemcpyAsync(op.d_runs, op.h_runs, rb, cudaMemcpyHostToDevice, st)) ||
+                !SFE_CUDA(cudaEventRecord(op.h_sched_done, st)))
+                return SFE_ERR_CUDA;
+            const int rc = launch_expand_sched(op.d_runs, (int)nr, op.d_sched, st);
+            if (rc != SFE_OK) return rc;
+            continue;
+        }
         // straight from the vector the walk filled, once its storage is registered (plan_call keeps it from moving)
         void *hp = op.sched.e.data();
         if (op.reg_ptr != hp) {
@@ -725,6 +766,8 @@ extern "C" void sfe_chain_destroy(sfe_chain *c)
         cudaFree(op.d_gp);
         cudaFree(op.d_bmat);
         cudaFree(op.d_sched);
+        cudaFree(op.d_runs);
+        if (op.h_runs) cudaFreeHost(op.h_runs);
         if (op.reg_ptr) cudaHostUnregister(op.reg_ptr);
         if (op.h_sched) cudaFreeHost(op.h_sched);
         if (op.h_sched_done) cudaEventDestroy(op.h_sched_done);

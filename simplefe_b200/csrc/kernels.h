@@ -130,5 +130,7 @@ int launch_bpsk_tx(const uint32_t *bits, long pitch_words, const uint64_t *hist_
 int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long pitch, long n, int H, int elem, int n_streams,
                      cudaStream_t st, bool overlap_prev = false);
 int launch_pack_dac10(const float *in, long n, uint8_t *out, cudaStream_t st);
+// d_out[run.k0 + j] <- entry j of every run (schedule.h: SchedRun)
+int launch_expand_sched(const SchedRun *d_runs, int n_runs, SchedEntry *d_out, cudaStream_t st);
 
 }  // namespace sfe

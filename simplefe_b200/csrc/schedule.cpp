@@ -105,6 +105,122 @@ int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t 
     return n_out;
 }
 
+// The same walk, recorded run by run (see SchedRun).  Every decision is the one walk_call takes -- the closed-form test,
+// the run length, the sequential fall-back -- only the per-output loop is gone.
+int walk_call_runs(WalkState &st, int up, int n_in, int out_len, float rate, int64_t base_in, RunVec &runs, int64_t *k)
+{
+    int n_out = 0;
+    const int64_t base = base_in * (int64_t)up;
+    float t = (float)st.pos + st.mu;
+    const float step = rate * (float)up;
+    const int64_t lim = (int64_t)n_in * up;
+    auto single = [&](int32_t pos, float mu) {
+        uint32_t mb;
+        memcpy(&mb, &mu, 4);
+        runs.push_back(SchedRun{*k, 1, pos, 0u, 0u, -1, mb});
+        (*k)++;
+    };
+    if (st.held) {
+        single((int32_t)(base - 1), st.mu);
+        n_out++;
+        st.held = false;
+        t = t + step;
+    }
+    {
+        int64_t room = out_len > n_out ? (int64_t)(out_len - n_out) : 0;
+        const int64_t most = lim + 2 + (st.pos < 0 ? -(int64_t)st.pos : 0);
+        if (room > most) room = most;
+        out_len = n_out + (int)room;
+    }
+    const int32_t base32 = (int32_t)base;
+    int pos = st.pos;
+    float mu = st.mu;
+    bool held = st.held;
+    for (;;) {
+        const float tf = t;
+        if (tf >= 1.0f && tf < 4194304.0f) {
+            uint32_t b0, b1, b2, b3;
+            const float t1 = tf + step, t2 = t1 + step, t3 = t2 + step;
+            memcpy(&b0, &tf, 4);
+            memcpy(&b1, &t1, 4);
+            memcpy(&b2, &t2, 4);
+            memcpy(&b3, &t3, 4);
+            if ((b3 >> 23) == (b0 >> 23)) {
+                const int e = (int)(b0 >> 23) - 127;
+                const uint32_t X0 = (b0 & 0x7FFFFFu) | 0x800000u, X1 = (b1 & 0x7FFFFFu) | 0x800000u;
+                const uint32_t X2 = (b2 & 0x7FFFFFu) | 0x800000u, X3 = (b3 & 0x7FFFFFu) | 0x800000u;
+                const uint32_t INC = X1 - X0;
+                if (INC > 0 && X2 - X1 == INC && X3 - X2 == INC) {
+                    const int sh = 23 - e;
+                    const uint32_t ub = (uint32_t)(e - 23 + 127) << 23;
+                    float u;
+                    memcpy(&u, &ub, 4);
+                    int64_t n_run = (int64_t)((0xFFFFFFu - X0) / INC);
+                    const int64_t L = lim > 1 ? ((lim - 1) << sh) : 0;
+                    const int64_t n_b = L > (int64_t)X0 ? (L - (int64_t)X0 + INC - 1) / INC : 0;
+                    if (n_b < n_run) n_run = n_b;
+                    if (out_len - n_out < n_run) n_run = out_len - n_out;
+                    if (n_run > 0) {
+                        const int nr = (int)n_run;
+                        runs.push_back(SchedRun{*k, nr, base32, X0, INC, sh, ub});
+                        *k += nr;
+                        n_out += nr;
+                        t = (float)(X0 + (uint32_t)nr * INC) * u;
+                        continue;
+                    }
+                }
+            }
+        }
+        pos = (int)tf;
+        if ((float)pos > tf) pos--;
+        mu = tf - (float)pos;
+        if (pos >= lim || n_out >= out_len) break;
+        if (pos + 1 >= lim) {
+            held = true;
+            break;
+        }
+        single(base32 + pos, mu);
+        n_out++;
+        t = tf + step;
+    }
+    st.pos = pos;
+    st.mu = mu;
+    st.held = held;
+    st.pos -= n_in * up;
+    return n_out;
+}
+
+int64_t walk_batch_runs(WalkState &st, int up, int blk, float rate, int64_t n_in, RunVec &runs)
+{
+    runs.clear();
+    const int out_len = (int)floorf((float)blk / rate) + 2;
+    int64_t k = 0;
+    for (int64_t off = 0; off < n_in; off += blk) {
+        const int n = (int)((n_in - off) < blk ? (n_in - off) : blk);
+        walk_call_runs(st, up, n, out_len, rate, off, runs, &k);
+    }
+    return k;
+}
+
+void expand_runs(const RunVec &runs, EntryVec &out)
+{
+    for (const SchedRun &r : runs) {
+        if (r.sh < 0) {
+            float mu;
+            memcpy(&mu, &r.ubits, 4);
+            out.push_back(SchedEntry{r.base, mu});
+            continue;
+        }
+        float u;
+        memcpy(&u, &r.ubits, 4);
+        const uint32_t fm = (1u << r.sh) - 1u;
+        for (int j = 0; j < r.n; j++) {
+            const uint32_t X = r.X0 + (uint32_t)j * r.INC;
+            out.push_back(SchedEntry{r.base + (int32_t)(X >> r.sh), (float)(X & fm) * u});
+        }
+    }
+}
+
 void walk_batch(WalkState &st, int up, int blk, float rate, int64_t n_in, Schedule &s, bool want_entries)
 {
     s.e.clear();

@@ -59,6 +59,29 @@ struct Schedule {
     float memo_rate = 0.f;
 };
 
+// A stretch of the walk in closed form (schedule.cpp): entry j < n of the run is
+//     X = X0 + j * INC;  pos = base + (X >> sh);  mu = (float)(X & ((1u << sh) - 1)) * u        (u = float with bits ubits)
+// i.e. the integer-mantissa arithmetic of one binade; sh < 0 marks a single entry {pos = base, mu = float(ubits)} that
+// went through the reference's own sequence (t < 1, the addition that leaves a binade, the end of a call).  A fractional-
+// rate schedule of 10^6 samples is a few thousand runs instead of 4 * 10^5 entries: the host walks run by run and the
+// device expands them (expand_sched_kernel), so neither the per-output host loop nor the 3 MB upload remain.
+struct SchedRun {
+    int64_t k0;           // index of the run's first output in the batch
+    int32_t n;            // outputs in the run
+    int32_t base;         // grid position offset (call offset * up), or the position itself for a single entry
+    uint32_t X0, INC;
+    int32_t sh;
+    uint32_t ubits;
+};
+typedef std::vector<SchedRun> RunVec;
+
+// walk_call with the outputs as runs: appends to `runs`, *k is the running output index of the batch
+int walk_call_runs(WalkState &st, int up, int n_in, int out_len, float rate, int64_t base_in, RunVec &runs, int64_t *k);
+// walk_batch for fractional steps, runs instead of entries; returns the number of outputs
+int64_t walk_batch_runs(WalkState &st, int up, int blk, float rate, int64_t n_in, RunVec &runs);
+// host expansion of a run list (tests; the device does the same in expand_sched_kernel)
+void expand_runs(const RunVec &runs, EntryVec &out);
+
 // One reference process() call: appends the outputs of a call with n_in samples whose first
 // sample sits at batch offset `base_in`; updates st.  Returns the number of outputs appended.
 int walk_call(WalkState &st, int up, int n_in, int out_len, float rate, int64_t base_in,

@@ -31,6 +31,26 @@ __global__ void save_tail_kernel(uint16_t *hn, const uint16_t *ho, const uint16_
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
+// Device-side expansion of a fractional-rate schedule: the host walks the reference's float32 recurrence run by run
+// (schedule.cpp, SchedRun: integer mantissa arithmetic inside one binade), the device turns every run into its entries.
+// Bit for bit the reference's sequence (tests/cpp/walk_diff.cxx expands the same runs on the host).
+__global__ void expand_sched_kernel(const SchedRun *runs, int n_runs, SchedEntry *out)
+{
+    for (int r = blockIdx.x; r < n_runs; r += gridDim.x) {
+        const SchedRun run = runs[r];
+        if (run.sh < 0) {
+            if (threadIdx.x == 0) out[run.k0] = SchedEntry{run.base, __uint_as_float(run.ubits)};
+            continue;
+        }
+        const float u = __uint_as_float(run.ubits);
+        const uint32_t fm = (1u << run.sh) - 1u;
+        for (int j = threadIdx.x; j < run.n; j += blockDim.x) {
+            const uint32_t X = run.X0 + (uint32_t)j * run.INC;
+            out[run.k0 + j] = SchedEntry{run.base + (int32_t)(X >> run.sh), __fmul_rn((float)(X & fm), u)};
+        }
+    }
+}
+
 // examples/bpsk/bpsk.cxx:76-101 / gr-simplefe/lib/sink_c_impl.cc:118-144:
 //   u = ((short)(x*511) + 512) & 0x3FF ; 4 words -> 5 bytes, the four 2-bit tops first
 __global__ void pack_dac10_kernel(const float *in, long n4, uint8_t *out)
@@ -77,6 +97,14 @@ int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long
     if (!SFE_CUDA(cudaLaunchKernelEx(&cfg, save_tail_kernel, static_cast<uint16_t *>(hist_new), static_cast<const uint16_t *>(hist_old),
                                      static_cast<const uint16_t *>(cur), pitch * u, n * u, H_u, n_streams)))
         return SFE_ERR_CUDA;
+    count_launch();
+    return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+}
+
+int launch_expand_sched(const SchedRun *d_runs, int n_runs, SchedEntry *d_out, cudaStream_t st)
+{
+    if (n_runs <= 0) return SFE_OK;
+    expand_sched_kernel<<<n_runs < 2368 ? n_runs : 2368, 128, 0, st>>>(d_runs, n_runs, d_out);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }

@@ -43,7 +43,7 @@ int main(int argc, char **argv)
 {
     std::mt19937 rng(argc > 1 ? atoi(argv[1]) : 1);
     const int iters = argc > 2 ? atoi(argv[2]) : 3000;
-    long cases = 0, entries = 0;
+    long cases = 0, entries = 0, run_total = 0;
     for (int it = 0; it < iters; it++) {
         const int up = 1 + rng() % 24;
         const int blk = 16 + rng() % 8192;
@@ -57,7 +57,9 @@ int main(int argc, char **argv)
             default: rate = 1.0f + (rng() % 4096) / 4096.0f * (rng() % 40); break;
         }
         if (rate * up < 1.0f) rate = 1.0f / up;
-        sfe::WalkState a, b;
+        sfe::WalkState a, b, r;
+        sfe::RunVec runs;
+        int64_t kr = 0;
         const int out_len = (int)floorf((float)blk / rate) + 2;
         sfe::EntryVec ea, eb;
         long off = 0;
@@ -65,6 +67,11 @@ int main(int argc, char **argv)
             const int n = (rng() % 4 == 0) ? 1 + (int)(rng() % blk) : blk;
             const int na = sfe::walk_call(a, up, n, out_len, rate, off, ea);
             const int nb = walk_seq(b, up, n, out_len, rate, off, eb);
+            const int nr = sfe::walk_call_runs(r, up, n, out_len, rate, off, runs, &kr);   // the run-recording flavour
+            if (nr != nb || r.pos != b.pos || memcmp(&r.mu, &b.mu, 4) || r.held != b.held || kr != (int64_t)eb.size()) {
+                printf("RUN MISMATCH (state) up %d blk %d rate %.9g call %d n %d: %d vs %d outputs\n", up, blk, rate, call, n, nr, nb);
+                return 1;
+            }
             if (na != nb || a.pos != b.pos || memcmp(&a.mu, &b.mu, 4) || a.held != b.held || ea.size() != eb.size() ||
                 memcmp(ea.data(), eb.data(), ea.size() * sizeof(sfe::SchedEntry))) {
                 printf("MISMATCH up %d blk %d rate %.9g call %d n %d: %d vs %d outputs\n", up, blk, rate, call, n, na, nb);
@@ -73,8 +80,15 @@ int main(int argc, char **argv)
             off += n;
             cases++;
         }
+        sfe::EntryVec er;
+        sfe::expand_runs(runs, er);
+        if (er.size() != eb.size() || memcmp(er.data(), eb.data(), er.size() * sizeof(sfe::SchedEntry))) {
+            printf("RUN MISMATCH (entries) up %d blk %d rate %.9g\n", up, blk, rate);
+            return 1;
+        }
+        run_total += (long)runs.size();
         entries += (long)ea.size();
     }
-    printf("ok: %ld calls, %ld entries identical\n", cases, entries);
+    printf("ok: %ld calls, %ld entries identical (walk_call, and %ld runs of walk_call_runs expanded)\n", cases, entries, run_total);
     return 0;
 }
