@@ -236,6 +236,24 @@ long sfe_rx_feed_pump(sfe_rx_feed *f, void *out, long cap, int wait_ms);
    4 the most output samples one block can produce (pump needs at least that much room in `out`) */
 long sfe_rx_feed_stat(sfe_rx_feed *f, int which);
 
+/* ---- (6) transmit side: float samples -> GPU DAC packing -> pinned byte ring -> device callback (additive) --------------- */
+/* The counterpart of the reference's sink blocks (gr-simplefe/lib/sink_c_impl.cc:84-174, sink_f_impl.cc): work() writes
+   float samples (a complex item is two floats), the USB thread's sfe_callback drains packed 10-bit DAC words.  The
+   packing (fill_tx_buffer, sink_c_impl.cc:118-144 = bpsk.cxx:76-101) runs on the GPU at write time; the ring holds wire
+   bytes in pinned memory.  One producer thread, one consumer thread. */
+typedef struct sfe_tx_feed sfe_tx_feed;
+sfe_tx_feed *sfe_tx_feed_create(int ring_bytes, int block_floats);   /* block_floats: most floats per write */
+void sfe_tx_feed_destroy(sfe_tx_feed *f);
+/* n <= block_floats floats; waits up to wait_ms for room in the ring (the reference's work() waits on a condition variable,
+   sink_c_impl.cc:165-169).  Returns n, 0 when there still was no room, or a negative status.  Up to 3 floats of an
+   unfinished quad are kept for the next write. */
+long sfe_tx_feed_write(sfe_tx_feed *f, const float *x, long n, int wait_ms);
+/* sfe_callback signature (libsimpleFE/simpleFE.h:42) for sfe_tx_start, `feed` as userdata: fills length/5*5 bytes, or
+   zeros the buffer and prints "U" on stderr when the ring holds fewer (sink_c_impl.cc:91-104) */
+int sfe_tx_feed_callback(unsigned char *buffer, int length, void *feed);
+/* which: 0 underflows ("U"), 1 bytes delivered, 2 bytes waiting, 3 floats a write can take now */
+long sfe_tx_feed_stat(sfe_tx_feed *f, int which);
+
 /* ---- sample format helpers (device wire formats) ---------------------- */
 /* float -> 10-bit DAC words, 4 samples -> 5 bytes: examples/bpsk/bpsk.cxx:76-101,
    gr-simplefe/lib/sink_c_impl.cc:118-144.  n must be a multiple of 4; device pointers. */

@@ -49,6 +49,10 @@ def _bind(lib):
         getattr(lib, f"sfeo_{k}_new").argtypes = [_f32p, ci, ci, ci]
         getattr(lib, f"sfeo_{k}_process").argtypes = [vp, _f32p, ci, _f32p, ci, cf]
         getattr(lib, f"sfeo_{k}_free").argtypes = [vp]
+    lib.sfeo_f32_to_dac10.argtypes = [_f32p, ci, C.c_void_p]
+    if hasattr(lib, "sfeo_ref_tx_packets"):
+        lib.sfeo_ref_tx_packets.restype = C.c_long
+        lib.sfeo_ref_tx_packets.argtypes = [_f32p, ci, ci, ci, C.c_void_p, C.c_long]
     lib.sfeo_i16_to_f32.argtypes = [C.c_void_p, _f32p, C.c_size_t]
     lib.sfeo_u8_to_f32.argtypes = [C.c_void_p, _f32p, C.c_size_t]
     lib.sfeo_chain_run.argtypes = [C.POINTER(_ChainCfg), C.c_void_p, ci, C.c_long, _f32p, C.c_long,
@@ -186,6 +190,31 @@ def u8_to_f32(x: np.ndarray, lib=None) -> np.ndarray:
     y = np.empty(x.shape, np.float32)
     lib.sfeo_u8_to_f32(x.ctypes.data, _fp(y), x.size)
     return y
+
+
+def f32_to_dac10(x: np.ndarray, lib=None) -> np.ndarray:
+    """float samples -> 10-bit DAC words, 4 samples -> 5 bytes (examples/bpsk/bpsk.cxx:76-101; the reference's own
+    convert_samples_to_bytes when oracle/_ref is loaded).  len(x) must be a multiple of 4."""
+    lib = lib or load()
+    x = np.ascontiguousarray(x, dtype=np.float32).ravel()
+    assert len(x) % 4 == 0
+    out = np.zeros(len(x) // 4 * 5, np.uint8)
+    n = lib.sfeo_f32_to_dac10(_fp(x), len(x), out.ctypes.data)
+    assert n == len(out)
+    return out
+
+
+def ref_tx_packets(x: np.ndarray, capacity: int, pkt: int, lib=None):
+    """reference only: ring_buffer<float>(capacity) filled with x, drained by bpsk.cxx's tx_callback in packets of
+    `pkt` bytes (bpsk.cxx:104-119); None when the loaded checker is the port"""
+    lib = lib or load()
+    if not hasattr(lib, "sfeo_ref_tx_packets"):
+        return None
+    x = np.ascontiguousarray(x, dtype=np.float32).ravel()
+    out = np.zeros(len(x) // 4 * 5 + pkt, np.uint8)
+    n = lib.sfeo_ref_tx_packets(_fp(x), len(x), int(capacity), int(pkt), out.ctypes.data, len(out))
+    assert n >= 0
+    return out[:n]
 
 
 IN_I16, IN_U8, IN_F32 = 0, 1, 2

@@ -92,6 +92,15 @@ int sfeo_resample_process(void *h, const float *in, int n_in, float *out, int ou
 void sfeo_resample_free(void *h) { delete static_cast<impl_resample *>(h); }
 
 /* ---- sample conversions (same expressions in both builds; see sfe_oracle.c for citations) -- */
+/* float -> 10-bit DAC words (examples/bpsk/bpsk.cxx:76-101): the reference's own convert_samples_to_bytes where the
+   reference is compiled in (ref_bpsk.cxx), its restatement otherwise.  n a multiple of 4; returns the bytes written. */
+#if defined(ORACLE_IMPL_REF)
+int sfeo_ref_f32_to_dac10(const float *in, int n, uint8_t *out);
+int sfeo_f32_to_dac10(const float *in, int n, uint8_t *out) { return sfeo_ref_f32_to_dac10(in, n, out); }
+#else
+int sfeo_f32_to_dac10(const float *in, int n, uint8_t *out) { return orc_f32_to_dac10(in, n, out); }
+#endif
+
 void sfeo_i16_to_f32(const int16_t *in, float *out, size_t n)
 {
     const float q = 1.0f / 32767.0f;

@@ -82,6 +82,11 @@ SYMBOLS = {
     "sfe_rx_feed_callback": (_ci, [_vp, _ci, _vp]),
     "sfe_rx_feed_pump": (_cl, [_vp, _vp, _cl, _ci]),
     "sfe_rx_feed_stat": (_cl, [_vp, _ci]),
+    "sfe_tx_feed_create": (_vp, [_ci, _ci]),
+    "sfe_tx_feed_destroy": (None, [_vp]),
+    "sfe_tx_feed_write": (_cl, [_vp, _f32p, _cl, _ci]),
+    "sfe_tx_feed_callback": (_ci, [_vp, _ci, _vp]),
+    "sfe_tx_feed_stat": (_cl, [_vp, _ci]),
     "sfe_ring_create": (_vp, [_ci, _ci]),
     "sfe_ring_alloc": (_ci, [_vp, _ci]),
     "sfe_ring_destroy": (None, [_vp]),

@@ -9,9 +9,14 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "kernels.h"
 
 namespace sfe {
+
+NvtxRange::NvtxRange(const char *name) { nvtxRangePushA(name); }
+NvtxRange::~NvtxRange() { nvtxRangePop(); }
 
 // ---- error / bookkeeping -----------------------------------------------------------------------
 static thread_local std::string g_err;

@@ -351,6 +351,7 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             if (!ensure(&w.mid[i], &w.mid_bytes[i], sizeof(float2) * (size_t)ns * dst_pitch)) return SFE_ERR_CUDA;
             dst = w.mid[i];
         }
+        const NvtxRange range(op.name.c_str());      // one range per op: its main kernel and its state carry
         const int eb = fmt_bytes(op.in_fmt);
         const char *hist_old = static_cast<const char *>(op.hist[c->cur]) + (size_t)s0 * op.H * eb;
         char *hist_new = static_cast<char *>(op.hist[c->cur ^ 1]) + (size_t)s0 * op.H * eb;
@@ -852,7 +853,10 @@ static int sfe_chain_process_dev_impl(sfe_chain *c, const void *d_in, long n_in,
     static const bool trace = getenv("SFE_TRACE_HOST") != nullptr;   // host time of the three parts of a call, on stderr
     const auto t0 = std::chrono::steady_clock::now();
     const WalkSnap snap = snapshot(c);
-    plan_call(c, n_in);
+    {
+        const NvtxRange range("sfe schedule walk");
+        plan_call(c, n_in);
+    }
     const auto t1 = std::chrono::steady_clock::now();
     const long no = c->ops.back().n_out;
     if (n_out) *n_out = no;

@@ -7,6 +7,7 @@
 // the ring is page-locked, and the consumer is the GPU: sfe_ring_read_dev moves whole blocks of bytes to the
 // device asynchronously and the chain's first kernel converts them while loading (SFE_IN_U8).
 #include <chrono>
+#include <cstring>
 #include <condition_variable>
 #include <mutex>
 
@@ -136,6 +137,144 @@ extern "C" long sfe_rx_feed_stat(sfe_rx_feed *f, int which)
         case 2: return f->bytes_in;
         case 3: return sfe_ring_count(f->ring);
         case 4: return f->out_cap;
+        default: return SFE_ERR_ARG;
+    }
+}
+
+// =====================================================================================================================
+// sfe_tx_feed_*: the transmit side (sink blocks).
+//
+// In the reference, sink_c/sink_f::work() write float samples into ring_buffer<T> under a mutex, waiting on a condition
+// variable for room (gr-simplefe/lib/sink_c_impl.cc:158-174), and the USB thread's tx_callback drains the ring through
+// fill_tx_buffer, which packs 4 samples into 5 bytes of 10-bit DAC words, or sends zeros and prints "U" when the ring
+// runs dry (sink_c_impl.cc:84-144; the same packing in examples/bpsk/bpsk.cxx:76-101).  Here the packing runs on the
+// GPU when the samples are written (sfe_pack_dac10 kernel) and the ring holds the finished wire bytes in pinned memory:
+// the USB thread's callback is a memcpy.
+namespace sfe {
+bool chain_device_ready(int *dev);
+}
+static int copy_bytes(void *dst, void *src, int n)
+{
+    memcpy(dst, src, (size_t)n);
+    return n;
+}
+static int same_len(int n) { return n; }
+
+struct sfe_tx_feed {
+    sfe_ring *ring = nullptr;      // packed DAC bytes
+    int block = 0;                 // most floats per write
+    float *h_in = nullptr;         // pinned staging: carry (<= 3 floats) + one write
+    uint8_t *h_out = nullptr;      // pinned staging of the packed bytes
+    float *d_in = nullptr;
+    uint8_t *d_out = nullptr;
+    float carry[4];
+    int n_carry = 0;               // floats of an unfinished quad kept for the next write
+    cudaStream_t st = nullptr;
+    std::mutex mu;
+    std::condition_variable cv;    // room was made (the reference's m_buf_cond)
+    long underflows = 0, bytes_out = 0;
+};
+
+extern "C" sfe_tx_feed *sfe_tx_feed_create(int ring_bytes, int block_floats)
+{
+    if (block_floats < 4 || ring_bytes < (block_floats / 4 + 1) * 5) {
+        set_error("tx_feed: block_floats >= 4 and a ring of at least one packed block (5 bytes per 4 samples)");
+        return nullptr;
+    }
+    int dev = 0;
+    if (!chain_device_ready(&dev)) return nullptr;
+    sfe_tx_feed *f = new sfe_tx_feed;
+    f->block = block_floats;
+    f->ring = sfe_ring_create(1, ring_bytes);
+    const size_t nf = (size_t)block_floats + 4, nb = nf / 4 * 5;
+    const bool ok = f->ring && SFE_CUDA(cudaStreamCreateWithFlags(&f->st, cudaStreamNonBlocking)) &&
+                    SFE_CUDA(cudaHostAlloc((void **)&f->h_in, sizeof(float) * nf, cudaHostAllocDefault)) &&
+                    SFE_CUDA(cudaHostAlloc((void **)&f->h_out, nb, cudaHostAllocDefault)) &&
+                    SFE_CUDA(cudaMalloc(&f->d_in, sizeof(float) * nf)) && SFE_CUDA(cudaMalloc(&f->d_out, nb));
+    if (!ok) {
+        sfe_tx_feed_destroy(f);
+        return nullptr;
+    }
+    return f;
+}
+
+extern "C" void sfe_tx_feed_destroy(sfe_tx_feed *f)
+{
+    if (!f) return;
+    if (f->st) cudaStreamSynchronize(f->st);
+    sfe_ring_destroy(f->ring);
+    if (f->h_in) cudaFreeHost(f->h_in);
+    if (f->h_out) cudaFreeHost(f->h_out);
+    cudaFree(f->d_in);
+    cudaFree(f->d_out);
+    if (f->st) cudaStreamDestroy(f->st);
+    delete f;
+}
+
+// producer: the role of sink_c_impl::work (sink_c_impl.cc:158-174).  n floats (a complex item is two); whole quads
+// are packed on the GPU and appended to the ring, up to 3 floats wait for the next write.  Blocks up to wait_ms for
+// room (the reference waits on its condition variable without limit); returns n, or 0 when there was no room.
+extern "C" long sfe_tx_feed_write(sfe_tx_feed *f, const float *x, long n, int wait_ms)
+{
+    if (!f || !x || n < 0 || n > f->block) {
+        set_error("tx_feed_write: 0 <= n <= block_floats");
+        return SFE_ERR_ARG;
+    }
+    const long tot = f->n_carry + n, quads = tot / 4, nb = quads * 5;
+    {
+        std::unique_lock<std::mutex> lk(f->mu);
+        auto room = [&] { return sfe_ring_space(f->ring) >= nb; };
+        if (!room() && wait_ms > 0) f->cv.wait_for(lk, std::chrono::milliseconds(wait_ms), room);
+        if (!room()) return 0;
+    }
+    memcpy(f->h_in, f->carry, sizeof(float) * f->n_carry);
+    memcpy(f->h_in + f->n_carry, x, sizeof(float) * n);
+    if (quads > 0) {
+        if (!SFE_CUDA(cudaMemcpyAsync(f->d_in, f->h_in, sizeof(float) * 4 * quads, cudaMemcpyHostToDevice, f->st))) return SFE_ERR_CUDA;
+        const int rc = launch_pack_dac10(f->d_in, 4 * quads, f->d_out, f->st);
+        if (rc != SFE_OK) return rc;
+        if (!SFE_CUDA(cudaMemcpyAsync(f->h_out, f->d_out, nb, cudaMemcpyDeviceToHost, f->st)) || !SFE_CUDA(cudaStreamSynchronize(f->st)))
+            return SFE_ERR_CUDA;
+        std::lock_guard<std::mutex> lk(f->mu);
+        if (sfe_ring_write(f->ring, f->h_out, (int)nb) != nb) {     // single producer: the room checked above is still there
+            set_error("tx_feed_write: ring refused a write it had room for (second producer?)");
+            return SFE_ERR_ARG;
+        }
+    }
+    f->n_carry = (int)(tot - 4 * quads);
+    memcpy(f->carry, f->h_in + 4 * quads, sizeof(float) * f->n_carry);
+    return n;
+}
+
+// consumer: sfe_callback signature, sink_c_impl::tx_callback / data_request (sink_c_impl.cc:84-104)
+extern "C" int sfe_tx_feed_callback(unsigned char *buffer, int length, void *feed)
+{
+    sfe_tx_feed *f = static_cast<sfe_tx_feed *>(feed);
+    if (!f || !buffer || length <= 0) return 0;
+    const int nb = length / 5 * 5;                       // the reference converts length/5 quads (calc_read_len, :107-111)
+    std::lock_guard<std::mutex> lk(f->mu);
+    if (sfe_ring_count(f->ring) < nb) {
+        memset(buffer, 0, (size_t)length);               // :95-97
+        fputc('U', stderr);
+        fflush(stderr);
+        f->underflows++;
+    } else {
+        sfe_ring_read(f->ring, buffer, (unsigned)nb, copy_bytes, same_len);
+        f->bytes_out += nb;
+        f->cv.notify_one();
+    }
+    return 0;
+}
+
+extern "C" long sfe_tx_feed_stat(sfe_tx_feed *f, int which)
+{
+    if (!f) return SFE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(f->mu);
+    switch (which) {
+        case 0: return f->underflows;
+        case 1: return f->bytes_out;
+        case 2: return sfe_ring_count(f->ring);
+        case 3: return (long)sfe_ring_space(f->ring) / 5 * 4 - f->n_carry;   // floats a write can take now
         default: return SFE_ERR_ARG;
     }
 }

@@ -27,6 +27,12 @@ void count_launch(int n = 1);
         return ret_on_throw;                                                                  \
     }
 
+// ---- NVTX ranges around the launches of one op (header-only NVTX 3: a no-op unless a profiler is attached) -----------
+struct NvtxRange {
+    explicit NvtxRange(const char *name);
+    ~NvtxRange();
+};
+
 // ---- complex helpers -------------------------------------------------------------------------
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }

@@ -36,6 +36,12 @@ def build(verbose=False):
                     os.path.join(HERE, "gr_block_check.cxx"), os.path.join(ROOT, "simplefe_b200", "gr", "gpu_source_c_impl.cc"),
                     "-o", exe_gr] + _link_flags(BIN), check=True)
     built.append(exe_gr)
+    # the sink blocks and the one-channel source (same stand-in headers)
+    exe_snk = os.path.join(BIN, "gr_sink_check")
+    subprocess.run(["g++", "-O2", "-std=c++11", "-pthread", "-I" + os.path.join(HERE, "stubs"), "-I" + os.path.join(ROOT, "include"),
+                    os.path.join(HERE, "gr_sink_check.cxx"), os.path.join(ROOT, "simplefe_b200", "gr", "gpu_sink_impl.cc"),
+                    os.path.join(ROOT, "simplefe_b200", "gr", "gpu_source_f_impl.cc"), "-o", exe_snk] + _link_flags(BIN), check=True)
+    built.append(exe_snk)
     if os.path.isdir(os.path.join(REF, "libdsp")):
         os.makedirs(REFOUT, exist_ok=True)
         exe2 = os.path.join(REFOUT, "test_blkconv_gpu")

@@ -15,12 +15,15 @@ class sync_block
 {
     std::string d_name;
     io_signature::sptr d_in, d_out;
+    long d_consumed = 0;
 
 public:
     sync_block() {}
     sync_block(const std::string &name, io_signature::sptr in, io_signature::sptr out) : d_name(name), d_in(in), d_out(out) {}
     virtual ~sync_block() {}
     virtual int work(int noutput_items, gr_vector_const_void_star &input_items, gr_vector_void_star &output_items) = 0;
+    void consume_each(int n) { d_consumed += n; }   // (a sync_block's scheduler bookkeeping; the check reads it back)
+    long consumed() const { return d_consumed; }
     const std::string &name() const { return d_name; }
     io_signature::sptr input_signature() const { return d_in; }
     io_signature::sptr output_signature() const { return d_out; }

@@ -12,11 +12,10 @@ def _impulses(bits, sps, amp):
     return x
 
 
-def _pack_ref(x):
-    u = ((x.astype(np.float32) * np.float32(511)).astype(np.int16).astype(np.int32) + 512) & 0x3FF
-    u = u.reshape(-1, 4)
-    return np.stack([(u[:, 0] >> 8) | ((u[:, 1] >> 8) << 2) | ((u[:, 2] >> 8) << 4) | ((u[:, 3] >> 8) << 6),
-                     u[:, 0] & 0xFF, u[:, 1] & 0xFF, u[:, 2] & 0xFF, u[:, 3] & 0xFF], axis=1).astype(np.uint8).ravel()
+def _unpack_codes(b):
+    """5 bytes -> four 10-bit codes (the inverse of bpsk.cxx:76-101), for counting code differences"""
+    b = b.reshape(-1, 5).astype(np.int32)
+    return np.stack([((b[:, 0] >> (2 * k)) & 3) << 8 | b[:, 1 + k] for k in range(4)], axis=1).ravel()
 
 
 def test_select_bits_follows_the_reference_block_structure():
@@ -62,11 +61,21 @@ def test_bpsk_tx_vs_reference_chain(gpu_lib, oracle_lib, tapname, sps, fft):
         ref = O.Blkconv(taps, fft, oracle_lib).filter(_impulses(allbits[c], sps, SCALING_FACTOR))[: y.shape[1]]
         nrms, peak = F.err_metrics(y[c], ref)
         assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (c, nrms, peak)
-    # fused DAC words: bit-exact packing of the kernel's own waveform, and within one code of the reference chain's
+    # fused DAC words.  (1) the kernel's packing of its own waveform is the reference's convert_samples_to_bytes
+    # (bpsk.cxx:76-101, compiled into oracle/_ref) bit for bit; (2) against the words of the REFERENCE chain
+    # (blkconv -> convert_samples_to_bytes): the two float waveforms differ by rounding (~1e-7), so a sample that sits
+    # on a code boundary of (short)(x*511) may land one code apart -- counted, bounded, never more than one code
     tx.reset()
     d = np.concatenate([tx.process(allbits[:, :n1], TX_DAC10), tx.process(allbits[:, n1:], TX_DAC10)], axis=1)
+    off_by_one = 0
     for c in range(C):
-        assert np.array_equal(d[c], _pack_ref(y[c]))
+        assert np.array_equal(d[c], O.f32_to_dac10(y[c], lib=oracle_lib))
+        ref = O.Blkconv(taps, fft, oracle_lib).filter(_impulses(allbits[c], sps, SCALING_FACTOR))[: y.shape[1]]
+        want = O.f32_to_dac10(ref, lib=oracle_lib)
+        dc = np.abs(_unpack_codes(d[c]) - _unpack_codes(want))
+        assert dc.max() <= 1, "never more than one DAC code from the reference chain's words"
+        off_by_one += int((dc == 1).sum())
+    assert off_by_one <= 1e-3 * C * y.shape[1], off_by_one   # boundary cases: a handful in 10^4 samples
     # one call == two calls (state carry), and a fresh object reproduces it
     one = BpskTx(taps, sps, C).process(allbits, TX_F32)
     assert np.array_equal(one, y)

@@ -244,15 +244,15 @@ def test_empty_and_tiny_inputs(gpu_lib):
     assert y.shape[1] in (0, 1)
 
 
-def test_dac10_packing(gpu_lib):
-    """float -> 10-bit DAC words, examples/bpsk/bpsk.cxx:76-101, integer exact"""
+def test_dac10_packing(gpu_lib, oracle_lib):
+    """float -> 10-bit DAC words, integer exact against the reference's own convert_samples_to_bytes
+    (examples/bpsk/bpsk.cxx:76-101, compiled verbatim into oracle/_ref; its restatement on boxes without the reference)"""
     import torch
+    from oracle import oracle as O
     rng = np.random.default_rng(1)
-    x = np.concatenate([rng.uniform(-1, 1, 4096), [1.0, -1.0, 0.0, 0.999]]).astype(np.float32)
-    u = ((x * np.float32(511)).astype(np.int16).astype(np.int32) + 512) & 0x3FF
-    u = u.reshape(-1, 4)
-    want = np.stack([(u[:, 0] >> 8) | ((u[:, 1] >> 8) << 2) | ((u[:, 2] >> 8) << 4) | ((u[:, 3] >> 8) << 6),
-                     u[:, 0] & 0xFF, u[:, 1] & 0xFF, u[:, 2] & 0xFF, u[:, 3] & 0xFF], axis=1).astype(np.uint8)
+    x = np.concatenate([rng.uniform(-1, 1, 4096), np.arange(-1022, 1023) / 1022.0, [1.0, -1.0, 0.0, 0.999]]).astype(np.float32)
+    x = x[: len(x) // 4 * 4]
+    want = O.f32_to_dac10(x, lib=oracle_lib).reshape(-1, 5)
     d_in = torch.from_numpy(x).cuda()
     d_out = torch.zeros(len(x) // 4 * 5, dtype=torch.uint8, device="cuda")
     assert gpu_lib.sfe_pack_dac10_dev(d_in.data_ptr(), len(x), d_out.data_ptr(), None) == 0

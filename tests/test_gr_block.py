@@ -64,6 +64,76 @@ def test_gr_block_sources_exist_and_mirror_the_reference_block():
         assert needle in hdr
     impl = open(os.path.join(HERE, "..", "simplefe_b200", "gr", "gpu_source_c_impl.cc")).read()
     assert "oracle" not in impl and "sfe_rx_feed_pump" in impl
+    # the other three block shapes of gr-simplefe (sink_c, sink_f, source_f) and their GRC descriptions
+    snk = open(os.path.join(HERE, "..", "include", "simplefe", "gpu_sink.h")).read()
+    for needle in ("class gpu_sink_c : virtual public gr::sync_block", "class gpu_sink_f : virtual public gr::sync_block",
+                   "boost::shared_ptr<gpu_sink_c> sptr", "boost::shared_ptr<gpu_sink_f> sptr", "tx_callback("):
+        assert needle in snk
+    srcf = open(os.path.join(HERE, "..", "include", "simplefe", "gpu_source_f.h")).read()
+    assert "class gpu_source_f : virtual public gr::sync_block" in srcf and "int channel" in srcf
+    for b in ("gpu_source_c", "gpu_source_f", "gpu_sink_c", "gpu_sink_f"):
+        xml = open(os.path.join(HERE, "..", "simplefe_b200", "gr", "grc", f"simplefe_{b}.xml")).read()
+        assert f"<key>simplefe_{b}</key>" in xml and f"simplefe.{b}(" in xml
+    for f in ("gpu_sink_impl.cc", "gpu_source_f_impl.cc"):
+        assert "oracle" not in open(os.path.join(HERE, "..", "simplefe_b200", "gr", f)).read()
+
+
+SINK_EXE = os.path.join(HERE, "cpp", "_bin", "gr_sink_check")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,pkt", [("sink_c", 500), ("sink_f", 1280), ("sink_f", 505)])
+def test_gr_sink_blocks_put_the_reference_bytes_on_the_wire(gpu_lib, oracle_lib, tmp_path, mode, pkt):
+    """work() in ragged item counts on one thread, tx_callback packets on another: the wire bytes are those of the
+    reference's fill_tx_buffer (sink_c_impl.cc:118-144 = bpsk.cxx:76-101) applied to the same samples, and -- where the
+    reference itself is compiled in -- those its own ring_buffer<float> + tx_callback (bpsk.cxx:104-119) deliver"""
+    from oracle import oracle as O
+    if not os.path.exists(SINK_EXE):
+        subprocess.run(["python", os.path.join(HERE, "cpp", "build_cpp.py")], check=True)
+    rng = np.random.default_rng(21)
+    n = 50003 if mode == "sink_f" else 2 * 25001
+    x = np.clip(rng.normal(0, 0.4, n), -1.0, 1.0).astype(np.float32)
+    x[:8] = [1.0, -1.0, 0.0, 0.5, -0.5, 0.999, -0.999, 1e-3]
+    (tmp_path / "in.f32").write_bytes(x.tobytes())
+    r = subprocess.run([SINK_EXE, mode, str(tmp_path / "in.f32"), str(tmp_path / "out.bytes"), str(pkt), "-"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "underflows 1" in r.stdout and r.stderr.count("U") == 1     # only the deliberate one
+    wire = np.fromfile(tmp_path / "out.bytes", np.uint8)
+    whole = len(x) // 4 * 4
+    want = O.f32_to_dac10(x[:whole], lib=oracle_lib)
+    n_pk = len(want) // pkt
+    assert len(wire) == n_pk * (pkt // 5 * 5) and n_pk > 10
+    assert np.array_equal(wire, want[: len(wire)])
+    ref = O.ref_tx_packets(x[:whole], whole + 8, pkt, lib=oracle_lib)
+    if ref is not None and pkt % 5 == 0:
+        assert np.array_equal(wire, ref[: len(wire)]), "same bytes as the reference's ring_buffer<float> + tx_callback"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["cfg2_small", "cfg5_small"])
+def test_gr_source_f_one_channel(gpu_lib, oracle_lib, tmp_path, name):
+    """one real channel (source_f_impl.cc:120-129: one byte per sample) through the chain: equals the reference classes
+    fed that channel's floats (the imaginary part of the stream is the format's zero and stays zero)"""
+    from oracle import oracle as O
+    if not os.path.exists(SINK_EXE):
+        subprocess.run(["python", os.path.join(HERE, "cpp", "build_cpp.py")], check=True)
+    cfg = dict(F.CONFIGS[name], in_fmt=F.IN_U8, S=1, N=24 * 4096)
+    iq = F.make_input(cfg)[0]
+    ch = np.ascontiguousarray(iq[:, 0])
+    x = np.stack([ch, np.full_like(ch, 128)], axis=1).reshape(1, -1, 2)
+    ref, _ = O.chain_run(x, F.IN_U8, cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib)
+    assert np.all(ref[0].imag == 0)
+    (tmp_path / "chain.bin").write_bytes(_chain_bytes(cfg))
+    (tmp_path / "in.u8").write_bytes(ch.tobytes())
+    n_items = len(ref[0])
+    r = subprocess.run([SINK_EXE, "source_f", str(tmp_path / "chain.bin"), str(tmp_path / "in.u8"), str(tmp_path / "out.f32"), str(n_items)],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    y = np.fromfile(tmp_path / "out.f32", np.float32)
+    assert y.shape == ref[0].real.shape
+    nrms, peak = F.err_metrics(y, ref[0].real)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (nrms, peak)
 
 
 @pytest.mark.gpu
