@@ -98,11 +98,11 @@ int main(int argc, char **argv)
         const std::vector<unsigned char> raw = slurp(argv[2]);
         const int pkt = atoi(argv[4]);
         if (mode == "sink_c") {
-            gr::simplefe::gpu_sink_c::sptr s = gr::simplefe::gpu_sink_c::make(8 * pkt, 2048);
+            gr::simplefe::gpu_sink_c::sptr s = gr::simplefe::gpu_sink_c::make(16384, 1024);
             if (s->name() != "gpu_sink_c") return 3;
             return run_sink(s, raw, 2, argv[3], pkt);
         }
-        gr::simplefe::gpu_sink_f::sptr s = gr::simplefe::gpu_sink_f::make(8 * pkt, 4096, 1);
+        gr::simplefe::gpu_sink_f::sptr s = gr::simplefe::gpu_sink_f::make(16384, 2048, 1);
         if (s->name() != "gpu_sink_f" || s->channel() != 1) return 3;
         return run_sink(s, raw, 1, argv[3], pkt);
     }
