@@ -326,7 +326,8 @@ def run_reference(args, name, cfg, rank, world):
 def workload_config(name, cfg, n_gpus, scaling):
     """identical in both arms (ours / reference): the driver compares the two `config` objects"""
     S = cfg["S"]
-    return {"workload": WORKLOADS[name][5], "streams_total": S, "samples_per_stream": cfg["N"],
+    fmt_name = {F.IN_I16: "int16 IQ", F.IN_U8: "u8 offset-binary IQ", F.IN_F32: "complex64"}[cfg["in_fmt"]]
+    return {"workload": WORKLOADS[name][5], "input_format": fmt_name, "streams_total": S, "samples_per_stream": cfg["N"],
             "streams_per_gpu": S // n_gpus if scaling == "strong" else S,
             "partition": f"independent streams split over {n_gpus} GPU(s) ({scaling}), no collective",
             "l2": "inputs larger than L2 (no flush needed)" if S * cfg["N"] * EB[cfg["in_fmt"]] // max(n_gpus, 1) > (256 << 20)
@@ -503,6 +504,8 @@ def main():
                                                               "instead of the batched one")
     ap.add_argument("--streams", type=int, default=0, help="total streams (default: the workload's)")
     ap.add_argument("--samples", type=int, default=0)
+    ap.add_argument("--in-fmt", default="", choices=["", "i16", "u8", "f32"], help="override the workload's input format "
+                    "(cfg1 i16 = the int16 IQ flavour of blkconv, 12 B/sample; cfg5 u8 = the device wire format)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
@@ -528,6 +531,8 @@ def main():
     fx, S_b, N_b, S_w, N_w, _ = WORKLOADS[name]
     S_def, N_def = (S_w, N_w) if args.as_worded else (S_b, N_b)
     cfg = dict(F.CONFIGS[fx], S=args.streams or S_def, N=args.samples or N_def)
+    if args.in_fmt:
+        cfg["in_fmt"] = {"i16": F.IN_I16, "u8": F.IN_U8, "f32": F.IN_F32}[args.in_fmt]
 
     if args.impl == "reference":
         run_reference(args, name, cfg, rank, world)

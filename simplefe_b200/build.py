@@ -42,6 +42,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = _nvcc()
     # tuning builds only: every K3 flavour of the variant sweeps (scripts/bank_sweep.sh); objects kept apart
     sweep = os.environ.get("SFE_BANK_SWEEP") == "1"
+    extra = os.environ.get("SFE_NVCC_EXTRA", "").split()     # tuning builds: extra -D flags (A/B runs on the GPU box)
     objdir = os.path.join(PKG, "build_sweep" if sweep else "build")
     os.makedirs(objdir, exist_ok=True)
     hdrs = [os.path.join(CSRC, h) for h in HEADERS]
@@ -53,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
             if src.endswith(".cu"):
-                cmd = [nvcc] + NVCC_FLAGS + (["-DSFE_BANK_SWEEP"] if sweep else []) + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+                cmd = [nvcc] + NVCC_FLAGS + (["-DSFE_BANK_SWEEP"] if sweep else []) + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
             else:
                 # host-only schedule code: as-written IEEE single precision, no FMA contraction
                 cmd = [nvcc, "-O2", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off",

@@ -19,6 +19,11 @@
 #include <cstdlib>
 #include <vector>
 
+// resident threads per SM the register allocation must allow (CTAs of <= 256 threads): 1024 = four 4096-point FFTs per SM
+// at 64 registers (no spills since the twiddle products replaced fifteen live table values by four)
+#ifndef SFE_K1_THREADS
+#define SFE_K1_THREADS 1024
+#endif
 #ifndef SFE_FFT_PACKED
 #define SFE_FFT_PACKED 1
 #endif
@@ -57,6 +62,12 @@ template <int N> struct Plan {
 };
 
 __device__ __forceinline__ int phi(int a) { return a + (a >> 4); }  // bank-conflict padding
+// padded index of element base + q*S: when S is a multiple of 16 the padding of the stride is a constant, so the compiler
+// keeps ONE address per thread and pass and folds q * (S + S/16) into the immediate offset of every LDS / STS
+template <int S> __device__ __forceinline__ int phi_at(int pbase, int base, int q)
+{
+    return S % 16 == 0 ? pbase + q * (S + S / 16) : phi(base + q * S);
+}
 
 // input flavours the kernel is compiled for (one instantiation each: no per-sample format dispatch)
 enum { KF_I16 = 0, KF_U8 = 1, KF_C64 = 2, KF_REAL = 3 };
@@ -107,6 +118,44 @@ template <int KF> __device__ __forceinline__ void store_output(const Ctx &c, int
     else reinterpret_cast<float2 *>(c.out_base)[i - c.p.ov] = v;
 }
 
+// ---- twiddles of one radix-16 pass ------------------------------------------------------------------------------
+// w[q] = exp(-2 pi i j q / M), q = 1..15.  Only the powers 1, 2, 4, 8 come from the table (one coalesced row piece each);
+// the other eleven are products of those, at most three multiplications deep (relative error < 3e-7, two orders inside
+// the parity budget).  With fifteen loads per thread and pass the twiddle rows were 18 % of this kernel's LSU
+// wavefronts, and the LSU data pipe is what bounds it (profiles/r02_ncu_k1_c64_before.json: 79.5 % of peak).
+#ifndef SFE_FFT_TW_PRODUCTS
+#define SFE_FFT_TW_PRODUCTS 1
+#endif
+__device__ __forceinline__ float2 cmul_pk(float2 a, float2 w)   // a * w as FMUL2 + FFMA2 (operand swizzles fold into the selectors)
+{
+    const cpx2 t = cmul2_pk(cpack(a), w);
+    return cunpack(t);
+}
+template <int S> __device__ __forceinline__ void load_twiddles(const float2 *row0, int j, float2 (&w)[16])
+{
+    // row0 = table row of q = 1 for this pass: row q-1 starts at row0 + (q-1) S
+#if SFE_FFT_TW_PRODUCTS
+    w[1] = __ldg(row0 + j);
+    w[2] = __ldg(row0 + S + j);
+    w[4] = __ldg(row0 + 3 * S + j);
+    w[8] = __ldg(row0 + 7 * S + j);
+    w[3] = cmul_pk(w[1], w[2]);
+    w[5] = cmul_pk(w[4], w[1]);
+    w[6] = cmul_pk(w[4], w[2]);
+    w[7] = cmul_pk(w[4], w[3]);
+    w[9] = cmul_pk(w[8], w[1]);
+    w[10] = cmul_pk(w[8], w[2]);
+    w[11] = cmul_pk(w[8], w[3]);
+    w[12] = cmul_pk(w[8], w[4]);
+    w[13] = cmul_pk(w[8], w[5]);
+    w[14] = cmul_pk(w[8], w[6]);
+    w[15] = cmul_pk(w[8], w[7]);
+#else
+#pragma unroll
+    for (int q = 1; q < 16; q++) w[q] = __ldg(row0 + (q - 1) * S + j);
+#endif
+}
+
 // ---- one forward (DIF) pass -------------------------------------------------------------------
 // P = pass index. FIRST: read from global. The last pass leaves its result in registers (vout).
 template <int N, int P, bool KEEP, int KF>
@@ -118,6 +167,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
     for (int u = 0; u < NB; u++) {
         const int beta = t + u * PL::TPF;
         const int b = (beta / S) * M, j = beta % S;
+        const int pb = phi(b + j);
         float2 v[R];
         if (P == 0) {
             if (c.in_interior) {   // all loads first, conversions after: R independent requests in flight per thread
@@ -132,19 +182,19 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
             }
         } else {
 #pragma unroll
-            for (int k = 0; k < R; k++) v[k] = X[phi(b + j + k * S)];
+            for (int k = 0; k < R; k++) v[k] = X[phi_at<S>(pb, b + j, k)];
         }
+        float2 w[16];
+        if constexpr (S > 1) load_twiddles<S>(c.p.tw + PL::tw_off(P), j, w);     // (S > 1 only in radix-16 passes)
         if (SFE_FFT_PACKED) dft_dif_packed<R, -1>(v);
         else dft_dif<R, -1>(v);
 #pragma unroll
         for (int sl = 0; sl < R; sl++) {
-            constexpr int dummy = 0;
-            (void)dummy;
             const int q = brev<R>(sl);
             float2 y = v[sl];
-            if (S > 1 && q != 0) y = cmul(y, __ldg(c.p.tw + PL::tw_off(P) + (q - 1) * S + j));
+            if (S > 1 && q != 0) y = cmul(y, w[q & 15]);
             if (KEEP) keep[u * R + q] = y;
-            else X[phi(b + j + q * S)] = y;
+            else X[phi_at<S>(pb, b + j, q)] = y;
         }
     }
 }
@@ -159,11 +209,14 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
     for (int u = 0; u < NB; u++) {
         const int beta = t + u * PL::TPF;
         const int b = (beta / S) * M, j = beta % S;
+        const int pb = phi(b + j);
         float2 v[R];
+        float2 w[16];
+        if constexpr (S > 1) load_twiddles<S>(c.p.tw + PL::tw_off(P), j, w);
 #pragma unroll
         for (int q = 0; q < R; q++) {
-            float2 y = FROMREG ? keep[u * R + q] : X[phi(b + j + q * S)];
-            if (S > 1 && q != 0) y = cmul_conj(y, __ldg(c.p.tw + PL::tw_off(P) + (q - 1) * S + j));
+            float2 y = FROMREG ? keep[u * R + q] : X[phi_at<S>(pb, b + j, q)];
+            if (S > 1 && q != 0) y = cmul_conj(y, w[q & 15]);
             v[q] = y;
         }
         if (SFE_FFT_PACKED) dft_dif_packed<R, +1>(v);
@@ -172,7 +225,7 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
         for (int sl = 0; sl < R; sl++) {
             const int k = brev<R>(sl);
             if (P == 0) store_output<KF>(c, b + j + k * S, v[sl]);
-            else X[phi(b + j + k * S)] = v[sl];
+            else X[phi_at<S>(pb, b + j, k)] = v[sl];
         }
     }
 }
@@ -257,8 +310,8 @@ template <int N> int launch_n(const BlkconvParams &p, cudaStream_t st)
     const long total = (long)p.n_streams * p.n_blocks;
     if (total <= 0) return SFE_OK;
     const size_t smem = sizeof(float2) * PL::PADN * FPB;
-    // resident CTAs per SM the register allocation must allow: 768 threads (85 registers each, no spills)
-    constexpr int MINB = PL::TPF * FPB <= 256 ? 768 / (PL::TPF * FPB) : 1;
+    // resident CTAs per SM the register allocation must allow (SFE_K1_THREADS)
+    constexpr int MINB = PL::TPF * FPB <= 256 ? SFE_K1_THREADS / (PL::TPF * FPB) : 1;
     void (*kern)(const BlkconvParams) =
         p.in_real ? blkconv_fft_kernel<N, FPB, MINB, KF_REAL>
                   : p.in.fmt == SFE_IN_I16 ? blkconv_fft_kernel<N, FPB, MINB, KF_I16>

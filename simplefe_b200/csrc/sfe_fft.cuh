@@ -113,6 +113,17 @@ __device__ __forceinline__ cpx2 csub2(cpx2 a, cpx2 b)
     return d;
 }
 
+// a * w with a packed, w = (wr, wi): (ar wr - ai wi, ai wr + ar wi) = a * (wr, wr) + (-ai, ar) * (wi, wi).  ptxas folds the
+// half swap, the negation and the broadcasts into the operand selectors of FMUL2 / FFMA2 (tests/probes/f32x2_sel_probe.cu).
+__device__ __forceinline__ cpx2 cmul2_pk(cpx2 a, float2 w)
+{
+    const float2 af = cunpack(a);
+    cpx2 t, d, wr = cpack(make_float2(w.x, w.x)), wi = cpack(make_float2(w.y, w.y)), sw = cpack(make_float2(-af.y, af.x));
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(a), "l"(wr));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(sw), "l"(wi), "l"(t));
+    return d;
+}
+
 template <int R, int SIGN, int HALF, int G, int I> struct dif2_inner {
     static __device__ __forceinline__ void run(cpx2 (&v)[R])
     {
