@@ -79,6 +79,7 @@ struct Op {
     int row_len = 0, n_rows = 0, rows_per_phase = 1, nc = 0, n_live = 1;
     long n_first = 0;
     bool bad_sched = false;
+    float lerp_tap = 0.f;          // OP_POLY with one tap and one phase: interpolation only (poly_lerp_kernel)
     bool direct_fir = false;       // OP_POLY standing in for blkconv: every sample is an output (pos = k, mu = 0)
     // per call
     long n_in = 0, n_out = 0;
@@ -465,6 +466,7 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             p.sched = op.d_sched;
             p.exact = (c->flags & SFE_FLAG_EXACT) ? 1 : 0;
             p.rate = op.rate;
+            p.lerp_tap = op.lerp_tap;
             rc = launch_poly_generic(p, st);
         }
         if (rc != SFE_OK) return rc;
@@ -590,6 +592,35 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
     int dev = 0;
     if (!chain_device_ready(&dev)) return nullptr;
 
+    // ---- blkconv followed by a one-phase (upsample 1) stage with a FRACTIONAL rate ------------------------------------
+    // With L = 1 the polyphase sum of decimate.cxx:132-140 is an ordinary causal FIR, s = a * y, and the stage's output
+    // is the linear interpolation (1-mu) s[pos] + mu s[pos+1] of it (decimate.cxx:123).  blkconv is a causal FIR too, so
+    // the FFT convolver applies g = h * a in one go -- at the cost it had for h alone -- and the stage that follows keeps
+    // only the interpolation: a polyphase stage with the single tap 1.  The schedule (rate, blk, held-over outputs) is
+    // untouched.  cfg 4: the 31-tap stage a was the most expensive kernel of the chain (1.27 of 2.7 ms).
+    sfe_chain_desc fused_desc;
+    std::vector<float> fused_taps;
+    static const float unit_tap = 1.0f;
+    bool lerp_fused = false;
+    {
+        long st = 0;
+        if (has_bc && has_a && d->a.up == 1 && !(d->flags & (SFE_FLAG_EXACT | SFE_FLAG_NO_FUSE)) && !integral_step(d->a, &st) &&
+            d->a.rate * (float)d->a.up == d->a.rate) {
+            std::vector<double> g((size_t)d->bc_ntaps + d->a.n_taps - 1, 0.0);
+            for (int i = 0; i < d->a.n_taps; i++)
+                for (int j = 0; j < d->bc_ntaps; j++) g[(size_t)i + j] += (double)d->a.taps[i] * (double)d->bc_taps[j];
+            while (g.size() > 1 && g.back() == 0.0) g.pop_back();
+            fused_taps.assign(g.begin(), g.end());
+            fused_desc = *d;
+            fused_desc.bc_taps = fused_taps.data();
+            fused_desc.bc_ntaps = (int)fused_taps.size();
+            fused_desc.a.taps = &unit_tap;
+            fused_desc.a.n_taps = 1;
+            d = &fused_desc;
+            lerp_fused = true;
+        }
+    }
+
     sfe_chain *c = new sfe_chain;
     c->dev = dev;
     c->S = d->n_streams;
@@ -676,7 +707,7 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
             op.tw = chain_twiddles(dev, op.N);
             op.hp = chain_spectrum(dev, d->bc_taps, d->bc_ntaps, op.N, nullptr);
             ok = ok && op.tw && op.hp;
-            op.name = "blkconv_fft" + std::to_string(op.N);
+            op.name = "blkconv_fft" + std::to_string(op.N) + (lerp_fused ? "(blkconv*stage_a_fir)" : "");
         } else {
             // taps longer than any compiled transform: direct FIR = one-phase polyphase stage with step 1
             op.kind = OP_POLY;
@@ -732,7 +763,13 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
             op.T = (int)t.size();
             op.H = (op.T - 1) / s.up + 1;
             ok = ok && upload(&op.d_taps, t);
-            c->plan += "polyphase_generic/L" + std::to_string(s.up) + "T" + std::to_string(op.T);
+            if (op.T == 1 && s.up == 1 && fmt == SFE_IN_F32 && !(d->flags & SFE_FLAG_EXACT)) {
+                op.lerp_tap = t[0];
+                op.H = 2;
+                c->plan += "lerp";
+            } else {
+                c->plan += "polyphase_generic/L" + std::to_string(s.up) + "T" + std::to_string(op.T);
+            }
         }
         op.name = c->plan.substr(plan_mark);
         c->ops.push_back(op);

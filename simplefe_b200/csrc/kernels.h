@@ -40,6 +40,7 @@ struct PolyParams {
     const SchedEntry *sched;  // device, n_out entries when !uniform
     int exact;            // reference operation order (separate multiply/add)
     float rate;           // the stage's rate (input samples per output): sizes the tile when the schedule is a table
+    float lerp_tap;       // != 0: the stage has this single tap (n_taps == 1, up == 1): pure interpolation kernel
     // filled by launch_poly_generic
     int kt, jp, tap_bytes, span_cap;
     int cw_bytes, grp_rows;   // K2s: bytes of combined taps per warp; rows of the grouped flavour's tap table (0 = one output at a time)

@@ -119,6 +119,25 @@ __global__ void __launch_bounds__(POLY_NT) poly_direct_kernel(const PolyParams p
     }
 }
 
+// One tap, one phase: the stage is the linear interpolation out[k] = tap * ((1-mu) x[pos] + mu x[pos+1]) of its input
+// (what remains of a fractional-rate decimator whose FIR was folded into the block convolver's taps, chain.cu).  Nothing
+// to stage and nothing to share: one thread per (stream, output), the two neighbouring samples straight from global
+// memory (a warp's reads cover one contiguous span of step * 32 samples), the schedule entry shared by all streams
+// through L1/L2.  HBM bound: reads about min(2, step)/step of the input once, writes the output once.
+__global__ void __launch_bounds__(256) poly_lerp_kernel(const PolyParams p, float tap)
+{
+    const long k = (long)blockIdx.x * 256 + threadIdx.x;
+    if (k >= p.n_out) return;
+    long pos;
+    float mu;
+    poly_sched(p, k, pos, mu);
+    const float w0 = tap * (1.0f - mu), w1 = tap * mu;
+    for (int s = blockIdx.y; s < p.n_streams; s += gridDim.y) {
+        const float2 a = load_sample(p.in, s, pos), b = load_sample(p.in, s, pos + 1);
+        reinterpret_cast<float2 *>(p.out)[(long)s * p.out_pitch + k] = make_float2(fmaf(w1, b.x, w0 * a.x), fmaf(w1, b.y, w0 * a.y));
+    }
+}
+
 // One CTA = p.kt consecutive outputs of one stream.  The input span those outputs touch and the taps (phase
 // major, tp[ph][j] = taps[ph + j*up], odd pitch) are staged in shared memory once; each thread then walks its
 // outputs' windows there, sharing every sample between the two interpolation points s(pos) and s(pos+1):
@@ -660,6 +679,12 @@ int launch_poly_generic(const PolyParams &p_in, cudaStream_t st)
 {
     PolyParams p = p_in;
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
+    if (p.n_taps == 1 && p.up == 1 && !p.exact && !p.in_real && p.lerp_tap != 0.f) {   // pure interpolation stage
+        dim3 grid((unsigned)((p.n_out + 255) / 256), (unsigned)(p.n_streams < 32768 ? p.n_streams : 32768));
+        poly_lerp_kernel<<<grid, 256, 0, st>>>(p, p.lerp_tap);
+        count_launch();
+        return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+    }
     // tile: as many outputs per CTA as keep the staged span under POLY_SPAN_BYTES (the span grows with the step)
     const int eb = p.in_real ? 4 : 8;
     const int J = (p.n_taps + p.up - 1) / p.up;
