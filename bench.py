@@ -393,16 +393,16 @@ def run_box(args, name, cfg):
         for g in range(G):
             torch.cuda.synchronize(g)
 
-    for _ in range(args.warmup):
-        n_out = step()
-    sync_all()
     sampler = ClockSampler(0)
-    sampler.start()
-    launches0 = lib.sfe_kernel_launches()
+    sampler.start()                                        # before the warm-up: no idle gap in front of the timed region
     ev = []
     for g in range(G):
         with torch.cuda.device(g):
             ev.append((torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)))
+    for _ in range(args.warmup):
+        n_out = step()
+    sync_all()
+    launches0 = lib.sfe_kernel_launches()
     w0 = time.time()
     for g in range(G):
         ev[g][0].record(streams[g])
@@ -510,7 +510,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the secondary weak-scaling figure")
-    ap.add_argument("--profile-every", type=int, default=5,
+    ap.add_argument("--profile-every", type=int, default=10,
                     help="bracket the kernels of every n-th timed step with CUDA events (0 = never).  A bracketed step cannot chain "
                          "its launch behind the previous call's (the event record sits between them), so it is a few us slower")
     ap.add_argument("--flags", type=int, default=0, help="SFE_FLAG_* for the chain (debug)")
@@ -585,15 +585,19 @@ def main():
         def step():   # one pass of the hot path over one batch: the next N samples of every stream
             return ch.process_dev(d_in.data_ptr(), N, N, d_out.data_ptr(), cap, stream.cuda_stream)
 
-        for _ in range(args.warmup):
-            n_out = step()
-        barrier()
-        # every fifth step is bracketed with events for the roofline; the others run as a caller's would (a bracketed
-        # step costs two event records and cannot start as a programmatic dependent of the previous call's kernel)
-        ch.profile(args.profile_every)
+        # The clock sampler needs 0.1-3 s to deliver its first line: it is started BEFORE the warm-up steps, so that the GPUs
+        # do not sit idle (and drop their clocks) between the warm-up and the timed region -- at 0.1 ms per step a timed
+        # region of K = 20 steps is 2 ms, shorter than a clock ramp.
         sampler = ClockSampler(local_rank)
         if rank == 0 and with_clocks:
             sampler.start()
+        barrier()
+        # every tenth step is bracketed with events for the roofline; the others run as a caller's would (a bracketed
+        # step costs two event records and cannot start as a programmatic dependent of the previous call's kernel)
+        ch.profile(0)
+        for _ in range(args.warmup):
+            n_out = step()
+        ch.profile(args.profile_every)
         launches0 = lib.sfe_kernel_launches()
         barrier()
         w0 = time.time()
@@ -635,7 +639,13 @@ def main():
             clocks["window"] = f"timed region ({(w1 - w0) * 1e3:.1f} ms) + untimed continuation of the same loop to {(w2 - w0) * 1e3:.0f} ms"
         barrier()
         prof = ch.profile_read()
-        return dict(ms=max_ranks(ms), ch=ch, d_in=d_in, d_out=d_out, cap=cap, n_out=n_out, launches=launches, prof=prof,
+        rank_ms = [ms]
+        if n_ranks > 1:           # every rank's own device time over the K steps: shows whether one rank is the straggler
+            tt = torch.zeros(n_ranks, dtype=torch.float64, device=dev)
+            tt[rank] = ms
+            dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+            rank_ms = [float(x) for x in tt.tolist()]
+        return dict(ms=max_ranks(ms), rank_ms=rank_ms, ch=ch, d_in=d_in, d_out=d_out, cap=cap, n_out=n_out, launches=launches, prof=prof,
                     clocks=clocks, host_us=host_s / args.steps * 1e6, small=small)
 
     # ---- the workload: streams split over the ranks (strong), or the full shard everywhere (weak) ---------------
@@ -788,7 +798,7 @@ def main():
         "dtype": "f32", "data": "synthetic", "config": workload_config(name, cfg, n_ranks, args.scaling),
         "plan": plan, "outputs_per_stream": int(n_out),
         "clocks": m["clocks"], "e2e": e2e, "gpu_launches": int(m["launches"]), "roofline": roofline, "parity": parity,
-        "host_enqueue_us_per_step": m["host_us"], "cpu_baseline": cpu,
+        "host_enqueue_us_per_step": m["host_us"], "rank_ms_per_step": [x / args.steps for x in m["rank_ms"]], "cpu_baseline": cpu,
     }
     if other is not None:
         line[other["scaling"]] = other
