@@ -392,6 +392,16 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             p.n_first = op.sched.pos0 >= 0 ? op.sched.pos0 / op.up : -1;
             rc = launch_decim_fir(p, st);
         } else if (op.kind == OP_TOEP && op.n_out > 0) {
+            // the kernel stages the rows by TMA, which needs 16-byte aligned rows: realign caller buffers that are not
+            if (((reinterpret_cast<uintptr_t>(src) & 15) || ((src_pitch * eb) & 15)) && op.n_in >= 128) {
+                const long ap = (op.n_in + 7) & ~7L;
+                if (!ensure(&w.d_align, &w.align_bytes, (size_t)ns * ap * eb)) return SFE_ERR_CUDA;
+                if (!SFE_CUDA(cudaMemcpy2DAsync(w.d_align, (size_t)ap * eb, src, (size_t)src_pitch * eb, (size_t)op.n_in * eb, ns,
+                                                cudaMemcpyDeviceToDevice, st)))
+                    return SFE_ERR_CUDA;
+                in.cur = w.d_align;
+                in.pitch = ap;
+            }
             ToepParams p{};
             p.in = in;
             p.out = static_cast<float2 *>(dst);

@@ -780,6 +780,50 @@ static bool seam_scratch(int dev, cudaStream_t st, size_t items, float2 **parts,
     return true;
 }
 
+}  // namespace sfe
+
+// Plain (unswizzled) 2-D map of rows of 32-bit words, box = box_cols x box_rows, out-of-range elements read as zero:
+// what the Toeplitz kernel stages its raw int16 IQ rows with.  Memoised like the bank kernel's maps.  `out` is a CUtensorMap.
+bool sfe_plain_map_2d(void *out, const void *base, long n_cols, long n_rows, long pitch_words, int box_cols, int box_rows)
+{
+    using namespace sfe;
+    static std::mutex mu;
+    static std::map<std::tuple<const void *, long, long, long, int, int>, CUtensorMap> cache;
+    const auto key = std::make_tuple(base, n_cols, n_rows, pitch_words, box_cols, box_rows);
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = cache.find(key);
+        if (it != cache.end()) {
+            *static_cast<CUtensorMap *>(out) = it->second;
+            return true;
+        }
+    }
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled is not available from this driver");
+        return false;
+    }
+    CUtensorMap m;
+    const cuuint64_t dims[2] = {(cuuint64_t)n_cols, (cuuint64_t)n_rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)pitch_words * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    const cuuint32_t es[2] = {1, 1};
+    const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void *>(base), dims, strides, box, es,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (plain 2-D) failed with CUresult " + std::to_string((int)r));
+        return false;
+    }
+    std::lock_guard<std::mutex> lk(mu);
+    if (cache.size() > 256) cache.clear();
+    cache[key] = m;
+    *static_cast<CUtensorMap *>(out) = m;
+    return true;
+}
+
+namespace sfe {
+
 static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
 {
     BankParams p = p_in;

@@ -75,6 +75,7 @@ struct ToepParams {
     float corr[3];        // 128 * sum_j d_tau[j]
     // filled by launch_toeplitz
     int ring, n_groups;
+    int n_stage, use_tma; // staging ring depth; 1: the raw rows are staged by TMA
     long n_steps;
 };
 struct ToepHost {

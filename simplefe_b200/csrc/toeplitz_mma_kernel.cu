@@ -16,15 +16,26 @@
 // arithmetic is exact; the only approximation is the 2^-23 (relative to the largest tap) tap quantisation.
 // The epilogue recombines  y = sum_tau w_tau * (256*(A_hi - 128*sum d_tau) + A_lo)  in fp32.
 //
-// Persistent, warp-specialised CTA (one per SM):
+// Persistent, warp-specialised CTA (two per SM):
 //   warps 0-3  epilogue   tcgen05.ld of the int32 accumulators, digit/byte recombination, float2 stores
 //   warp  4    MMA issue  one thread; tcgen05.mma.cta_group::1.kind::i8, commits to mbarriers
-//   warps 5-12 producers  128-bit global loads of int16 IQ, byte-plane split with PRMT, stores into the
-//                         K-major SWIZZLE_128B operand tiles of a shared-memory ring (no im2col copy:
-//                         consecutive steps reuse KB-1 of their KB K-block tiles)
+//   warp  5    TMA issue  one thread; the raw int16 IQ rows of a K-block (32 streams x 128 samples = 16 KB) as ONE
+//                         cp.async.bulk.tensor box into a staging ring, several K-blocks ahead
+//   warps 6-13 producers  128-bit shared-memory loads of the staged rows, byte-plane split with PRMT, stores into the
+//                         K-major SWIZZLE_128B operand tiles of a second ring (no im2col copy: consecutive steps
+//                         reuse KB-1 of their KB K-block tiles).  Round 1 loaded the rows with LDG into registers: the
+//                         producers then spent 70 % of their 1650 warp instructions per step on 64-bit row addresses,
+//                         bounds checks and rematerialised swizzle offsets (72-register cap), and a third of all stall
+//                         samples on those loads' scoreboard (profiles/r02_k2t_summary.json).  K-blocks that reach
+//                         into the history rows (the first of a call) still take that path.
+#include <cuda.h>
+
 #include <cstdlib>
+#include <cstring>
 
 #include "kernels.h"
+
+bool sfe_plain_map_2d(void *out, const void *base, long n_cols, long n_rows, long pitch_words, int box_cols, int box_rows);
 
 namespace sfe {
 
@@ -36,9 +47,9 @@ constexpr int TNT = 3;             // tap digits
 constexpr int TNCOL = TNT * TNO;   // 48 accumulator columns
 constexpr int TILE_BYTES = 128 * 128;
 constexpr int N_EPI_WARPS = 4, N_PROD_WARPS = 8;
-constexpr int N_THREADS = 32 * (N_EPI_WARPS + 1 + N_PROD_WARPS);
-constexpr int MAX_RING = 12;
-constexpr int TPF = 2;              // producer prefetch depth (K-blocks in flight per warp)
+constexpr int W_MMA = N_EPI_WARPS, W_TMA = N_EPI_WARPS + 1, W_PROD0 = N_EPI_WARPS + 2;
+constexpr int N_THREADS = 32 * (N_EPI_WARPS + 2 + N_PROD_WARPS);
+constexpr int MAX_RING = 12, MAX_STAGE = 6;
 constexpr int ACC_STRIDE = 64;     // TMEM columns between the two accumulators
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -57,6 +68,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
     while (!done)
         asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
                      : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_rows(uint32_t dst, const CUtensorMap *map, int x, int y, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar)
 {
@@ -106,16 +126,18 @@ __device__ __forceinline__ uint32_t load_i16(const ToepParams &p, int s, long n)
     return h < 0 ? 0u : __ldg(reinterpret_cast<const uint32_t *>(p.in.hist) + (long)s * p.in.H + h);
 }
 
-__global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const ToepParams p)
+__global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_constant__ CUtensorMap map_cur, const ToepParams p)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bar_full[MAX_RING], bar_empty[MAX_RING], bar_acc_full[2], bar_acc_empty[2];
+    __shared__ __align__(8) uint64_t bar_st_full[MAX_STAGE], bar_st_empty[MAX_STAGE];
     __shared__ uint32_t tmem_base_s;
 
-    const int KB = p.KB, R = p.ring;
+    const int KB = p.KB, R = p.ring, Q = p.n_stage;
     uint8_t *sbase = smem + ((1024u - (smem_u32(smem) & 1023u)) & 1023u);   // SWIZZLE_128B tiles need 1024 B alignment
     uint8_t *sB = sbase;                                  // KB tiles of TNCOL rows x 128 B (swizzled image)
     uint8_t *ring = sbase + ((KB * TNCOL * 128 + 1023) & ~1023);  // R tiles of 128 rows x 128 B
+    uint8_t *stage = ring + (size_t)R * TILE_BYTES;       // Q tiles of 32 rows x 512 B: raw int16 IQ of one K-block
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     // ---- one-time setup ---------------------------------------------------------------------------
@@ -131,9 +153,13 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const ToepPar
             mbar_init(&bar_acc_full[i], 1);
             mbar_init(&bar_acc_empty[i], 32 * N_EPI_WARPS);
         }
+        for (int i = 0; i < Q; i++) {
+            mbar_init(&bar_st_full[i], 1);
+            mbar_init(&bar_st_empty[i], 32 * N_PROD_WARPS);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == N_EPI_WARPS) {
+    if (warp == W_MMA) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(128));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
@@ -144,40 +170,55 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const ToepPar
 
     const long X0 = p.n_first - 128L * (KB - 1);          // first sample of K-block 0
 
-    if (warp > N_EPI_WARPS) {
+    // a K-block is staged by TMA when it lies in the current rows (the TMA zero-fills what is behind their end and the
+    // rows of a ragged last group); K-blocks that reach into the history rows are loaded by the producers themselves
+    const bool use_tma = p.use_tma != 0;
+    auto staged = [&](long m) -> bool { return use_tma && X0 + 128 * m >= 0; };
+
+    if (warp == W_TMA) {
+        // =================================== TMA issuer =============================================
+        if (lane == 0) {
+            int q_slot = 0;
+            uint32_t q_par = 0;
+            PieceIter it(p);
+            Piece pc;
+            while (it.next(pc)) {
+                const long m_end = pc.j1 + KB - 1;
+                for (long m = pc.j0; m < m_end; m++) {
+                    if (!staged(m)) continue;
+                    mbar_wait(&bar_st_empty[q_slot], q_par ^ 1);                 // every producer has read the slot
+                    mbar_expect_tx(&bar_st_full[q_slot], TILE_BYTES);
+                    tma_rows(smem_u32(stage) + (uint32_t)q_slot * TILE_BYTES, &map_cur, (int)(X0 + 128 * m), pc.g * 32, &bar_st_full[q_slot]);
+                    if (++q_slot == Q) { q_slot = 0; q_par ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= W_PROD0) {
         // =================================== producers ==============================================
-        const int pw = warp - N_EPI_WARPS - 1;
-        const bool aligned = ((X0 & 3) == 0) && ((p.in.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.in.cur) & 15) == 0);
-        int p_slot = 0;
-        uint32_t p_par = 0;
-        const uint32_t ring_sa = smem_u32(ring);
+        const int pw = warp - W_PROD0;
+        int p_slot = 0, q_slot = 0;
+        uint32_t p_par = 0, q_par = 0;
+        const uint32_t ring_sa = smem_u32(ring), stage_sa = smem_u32(stage);
         uint32_t soff[4];                                  // swizzled byte offsets of this thread's four plane rows (q = 0)
 #pragma unroll
         for (int k = 0; k < 4; k++) soff[k] = swz(4 * pw + k, 4 * lane);
+        const uint32_t st_off = (uint32_t)pw * 512u + (uint32_t)lane * 16u;   // this lane's 4 samples of staged row pw (+ 8 q rows)
         PieceIter it(p);
         Piece pc;
         while (it.next(pc)) {
             const int s_base = pc.g * 32;
-            // The loads of step m + PF are issued before step m is split and stored: PF K-blocks (2 KB per warp each)
-            // stay in flight per warp.  Without this a warp holds one step's loads at a time and the whole CTA moves
-            // 16 KB per HBM round trip (measured 1.37 us per step; tensor pipe 7 % busy).
-            // per piece: row pointers of this warp's four streams; per step only the sample offset moves
-            const uint32_t *rowp[4];
-            bool row_ok[4];
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const int s = s_base + pw + 8 * q;
-                row_ok[q] = s < p.n_streams;
-                rowp[q] = reinterpret_cast<const uint32_t *>(p.in.cur) + (long)(row_ok[q] ? s : 0) * p.in.pitch;
-            }
-            auto load_step = [&](long m, uint4 (&v)[4]) {
-                const long nb = X0 + 128 * m;              // first sample of the K-block (warp uniform)
-                const long n0 = nb + 4 * lane;             // this lane's 4 samples
-                if (aligned && nb >= 0 && nb + 128 <= p.in.n) {   // whole block inside the current rows
+            const long m_end = pc.j1 + KB - 1;
+            for (long m = pc.j0; m < m_end; m++) {
+                uint4 v[4];
+                if (staged(m)) {
+                    mbar_wait(&bar_st_full[q_slot], q_par);
+                    const uint32_t sa = stage_sa + (uint32_t)q_slot * TILE_BYTES + st_off;
 #pragma unroll
                     for (int q = 0; q < 4; q++)
-                        v[q] = row_ok[q] ? __ldg(reinterpret_cast<const uint4 *>(rowp[q] + n0)) : make_uint4(0u, 0u, 0u, 0u);
+                        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                     : "=r"(v[q].x), "=r"(v[q].y), "=r"(v[q].z), "=r"(v[q].w) : "r"(sa + q * 4096));
                 } else {
+                    const long n0 = X0 + 128 * m + 4 * lane;
 #pragma unroll
                     for (int q = 0; q < 4; q++) {
                         const int s = s_base + pw + 8 * q;
@@ -187,8 +228,6 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const ToepPar
                         v[q].w = load_i16(p, s, n0 + 3);
                     }
                 }
-            };
-            auto store_step = [&](const uint4 (&v)[4]) {
                 const int slot = p_slot;                   // ring position and lap parity advance without divisions
                 const uint32_t par = p_par;
                 if (++p_slot == R) { p_slot = 0; p_par ^= 1; }
@@ -208,23 +247,13 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const ToepPar
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&bar_full[slot]);
-            };
-            const long m_end = pc.j1 + KB - 1;
-            uint4 v[TPF][4];
-#pragma unroll
-            for (int u = 0; u < TPF; u++)
-                if (pc.j0 + u < m_end) load_step(pc.j0 + u, v[u]);
-            for (long m = pc.j0; m < m_end; m += TPF) {
-#pragma unroll
-                for (int u = 0; u < TPF; u++) {
-                    if (m + u < m_end) {
-                        store_step(v[u]);
-                        if (m + u + TPF < m_end) load_step(m + u + TPF, v[u]);
-                    }
+                if (staged(m)) {                           // the staged rows are in registers (and split): the slot may be refilled
+                    mbar_arrive(&bar_st_empty[q_slot]);
+                    if (++q_slot == Q) { q_slot = 0; q_par ^= 1; }
                 }
             }
         }
-    } else if (warp == N_EPI_WARPS) {
+    } else if (warp == W_MMA) {
         // =================================== MMA issuer ==============================================
         if (lane == 0) {
             const uint32_t idesc = (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t)(TNCOL >> 3) << 17) | ((128u >> 4) << 24);
@@ -336,7 +365,7 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const ToepPar
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     __syncwarp();
-    if (warp == N_EPI_WARPS) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(128));
+    if (warp == W_MMA) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(128));
 }
 
 }  // namespace
@@ -349,23 +378,46 @@ int launch_toeplitz(const ToepParams &p_in, cudaStream_t st)
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
     p.n_groups = (p.n_streams + 31) / 32;
     p.n_steps = (p.n_out + TNO - 1) / TNO;
-    p.ring = p.KB + 4 <= MAX_RING ? p.KB + 4 : MAX_RING;
     if (p.KB < 1 || p.KB + 2 > MAX_RING || p.in.fmt != SFE_IN_I16) {
         set_error("toeplitz_i8: unsupported configuration");
         return SFE_ERR_ARG;
     }
-    const size_t smem = ((size_t)(p.KB * TNCOL * 128 + 1023) & ~(size_t)1023) + (size_t)p.ring * TILE_BYTES + 1024;
+    // The raw rows are staged by TMA when the caller's rows can carry a tensor map (16-byte aligned base and pitch).
+    // Shared memory per CTA: tap tiles + operand ring (>= KB + 1 tiles) + staging ring; two CTAs per SM when that fits.
+    CUtensorMap map;
+    memset(&map, 0, sizeof map);
+    static const bool no_tma = getenv("SFE_TOEP_NO_TMA") != nullptr;       // tuning hook: producers load from global memory
+    p.use_tma = !no_tma && (reinterpret_cast<uintptr_t>(p.in.cur) & 15) == 0 && (p.in.pitch & 3) == 0 && p.in.n >= 128;
+    if (p.use_tma && !sfe_plain_map_2d(&map, p.in.cur, p.in.n, p.n_streams, p.in.pitch, 128, 32)) return SFE_ERR_CUDA;
+    static const int stage_env = getenv("SFE_TOEP_STAGE") ? atoi(getenv("SFE_TOEP_STAGE")) : 0;   // tuning hook: staging depth
+    const size_t b_bytes = ((size_t)(p.KB * TNCOL * 128 + 1023) & ~(size_t)1023);
+    auto smem_for = [&](int ring, int stage) { return b_bytes + (size_t)(ring + stage) * TILE_BYTES + 1024; };
+    p.n_stage = p.use_tma ? (stage_env > 0 ? stage_env : 3) : 1;
+    if (p.n_stage > MAX_STAGE) p.n_stage = MAX_STAGE;
+    p.ring = p.KB + 1;
+    // spend what two CTAs per SM leave on the operand ring first (up to KB + 4), then fall back to one CTA
+    const size_t two_cta = (227 * 1024) / 2 - 2048;
+    while (p.ring < p.KB + 4 && p.ring < MAX_RING && smem_for(p.ring + 1, p.n_stage) <= two_cta) p.ring++;
+    if (smem_for(p.ring, p.n_stage) > two_cta) {            // one CTA per SM: room for a deep ring
+        p.ring = p.KB + 4 <= MAX_RING ? p.KB + 4 : MAX_RING;
+        while (smem_for(p.ring, p.n_stage) > 225 * 1024 && p.n_stage > 1) p.n_stage--;
+    }
+    const size_t smem = smem_for(p.ring, p.n_stage);
+    if (smem > 227 * 1024) {
+        set_error("toeplitz_i8: tap count too large for shared memory");
+        return SFE_ERR_ARG;
+    }
     if (!SFE_CUDA(cudaFuncSetAttribute(toeplitz_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
     int dev = 0, sms = 0;
     if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
     const long F = (long)p.n_groups * p.n_steps;
     long grid = F / 4 > 0 ? F / 4 : 1;                    // at least ~4 steps per CTA
-    // two CTAs per SM when their rings fit (72 registers x 416 threads and 128 TMEM columns each): the second CTA's warps
+    // two CTAs per SM when their rings fit (72 registers x 448 threads and 128 TMEM columns each): the second CTA's warps
     // fill the issue slots the first one leaves while its producers, MMA thread and epilogue wait on each other
     static const bool one_cta = getenv("SFE_TOEP_ONE_CTA") != nullptr;   // tuning hook
     const int per_sm = (2 * (smem + 2048) <= 227 * 1024 && !one_cta) ? 2 : 1;
     if (grid > (long)sms * per_sm) grid = (long)sms * per_sm;
-    toeplitz_i8_kernel<<<(unsigned)grid, N_THREADS, smem, st>>>(p);
+    toeplitz_i8_kernel<<<(unsigned)grid, N_THREADS, smem, st>>>(map, p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }
