@@ -378,7 +378,7 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             p.hp = op.hp;
             p.mode = BLKCONV_MODE_CONV;
             rc = launch_blkconv(op.N, p, st);
-        } else if (op.kind == OP_DECIM && op.n_out > 0) {
+        } else if ((op.kind == OP_DECIM || (op.kind == OP_TOEP && op.d_gp && op.n_out < 4 * 1024)) && op.n_out > 0) {
             DecimParams p{};
             p.in = in;
             p.out = static_cast<float2 *>(dst);
@@ -760,11 +760,15 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
             } else {
                 c->plan += "decim_fir";
             }
+            // tensor cores: many streams sharing the filter, or ONE long stream (its row is time-split over the tile rows;
+            // short calls of a single stream fall back to the CUDA-core FIR at run time, so that op carries both tap images)
             const bool tensor = !(d->flags & SFE_FLAG_NO_TENSOR) && fmt == SFE_IN_I16 && step / s.up == 8 &&
-                                d->n_streams >= 8 && (int)g.size() <= toeplitz_max_taps();
+                                (d->n_streams >= 8 || d->n_streams == 1) && (int)g.size() <= toeplitz_max_taps();
+            const bool both = tensor && d->n_streams == 1;
+            if (both) ok = ok && make_decim(op, g, (int)(step / s.up));
             if (tensor && make_toep(op, g)) {
-                c->plan += "[toeplitz_i8_tcgen05]";
-            } else {
+                c->plan += both ? "[toeplitz_i8_tcgen05 time-split | decim_fir for short calls]" : "[toeplitz_i8_tcgen05]";
+            } else if (!both) {
                 ok = ok && make_decim(op, g, (int)(step / s.up));
             }
             c->plan += "/D" + std::to_string(op.D) + "T" + std::to_string(op.T);

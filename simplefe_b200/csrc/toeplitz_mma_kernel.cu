@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
 
 int toeplitz_max_taps() { return 128 * (MAX_RING - 4 - 1) + 1; }
 
-int launch_toeplitz(const ToepParams &p_in, cudaStream_t st)
+static int launch_toeplitz_rows(const ToepParams &p_in, cudaStream_t st)
 {
     ToepParams p = p_in;
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
@@ -387,7 +387,10 @@ int launch_toeplitz(const ToepParams &p_in, cudaStream_t st)
     CUtensorMap map;
     memset(&map, 0, sizeof map);
     static const bool no_tma = getenv("SFE_TOEP_NO_TMA") != nullptr;       // tuning hook: producers load from global memory
-    p.use_tma = !no_tma && (reinterpret_cast<uintptr_t>(p.in.cur) & 15) == 0 && (p.in.pitch & 3) == 0 && p.in.n >= 128;
+    // (a box must start on a 16-byte boundary of its row: calls whose first output does not sit on a multiple of four samples
+    // -- a stream fed in pieces that are not multiples of 8 samples -- keep the producers' own loads)
+    p.use_tma = !no_tma && (reinterpret_cast<uintptr_t>(p.in.cur) & 15) == 0 && (p.in.pitch & 3) == 0 && p.in.n >= 128 &&
+                ((p.n_first - 128L * (p.KB - 1)) & 3) == 0;
     if (p.use_tma && !sfe_plain_map_2d(&map, p.in.cur, p.in.n, p.n_streams, p.in.pitch, 128, 32)) return SFE_ERR_CUDA;
     static const int stage_env = getenv("SFE_TOEP_STAGE") ? atoi(getenv("SFE_TOEP_STAGE")) : 0;   // tuning hook: staging depth
     const size_t b_bytes = ((size_t)(p.KB * TNCOL * 128 + 1023) & ~(size_t)1023);
@@ -420,6 +423,46 @@ int launch_toeplitz(const ToepParams &p_in, cudaStream_t st)
     toeplitz_i8_kernel<<<(unsigned)grid, N_THREADS, smem, st>>>(map, p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+}
+
+// ONE long stream (BASELINE.json cfg 2 as it is worded: a single 10 MS/s channel) would fill 1 of the 32 stream rows of
+// every tile.  The FIR is time invariant, so the row is cut into pieces of Kp outputs (Q = 8 Kp samples) that run as the
+// ROWS of one launch: piece r starts 128 KB samples before its first new sample (its "history" is simply the preceding
+// part of the row: overlapping rows, pitch Q), piece 0 keeps the call's real history, and what is left behind the last
+// whole piece runs as a third, one-row launch.  Same tiles, same taps, same summation order as the unsplit launch.
+int launch_toeplitz(const ToepParams &p, cudaStream_t st)
+{
+    static const bool no_split = getenv("SFE_TOEP_NO_SPLIT") != nullptr;   // tuning hook
+    const long Kp = 1024, Q = TD * Kp, B = 128L * p.KB;
+    const long P = p.n_out / Kp;
+    if (p.n_streams != 1 || no_split || P < 4 || p.in.fmt != SFE_IN_I16) return launch_toeplitz_rows(p, st);
+    ToepParams a = p;                        // piece 0: the real history
+    a.n_out = Kp;
+    int rc = launch_toeplitz_rows(a, st);
+    if (rc != SFE_OK) return rc;
+    ToepParams b = p;                        // pieces 1 .. P-2 as rows
+    b.in.cur = static_cast<const uint32_t *>(p.in.cur) + (Q - B);
+    b.in.hist = b.in.cur;
+    b.in.H = 0;
+    b.in.pitch = Q;
+    b.in.n = B + Q + 16;                     // every sample a piece touches lies inside the original row
+    b.n_first = p.n_first + B;
+    b.n_streams = (int)(P - 2);
+    b.n_out = Kp;
+    b.out = p.out + Kp;
+    b.out_pitch = Kp;
+    rc = launch_toeplitz_rows(b, st);
+    if (rc != SFE_OK) return rc;
+    ToepParams c = b;                        // the rest: one row from the start of piece P-1
+    c.in.cur = static_cast<const uint32_t *>(p.in.cur) + ((P - 1) * Q - B);
+    c.in.hist = c.in.cur;
+    c.in.n = p.in.n - ((P - 1) * Q - B);
+    c.in.pitch = (c.in.n + 3) & ~3L;
+    c.n_streams = 1;
+    c.n_out = p.n_out - (P - 1) * Kp;
+    c.out = p.out + (P - 1) * Kp;
+    c.out_pitch = c.n_out;
+    return launch_toeplitz_rows(c, st);
 }
 
 // Host side: quantise g to 24-bit fixed point, split into three signed base-256 digits and lay the banded
