@@ -760,11 +760,11 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
             } else {
                 c->plan += "decim_fir";
             }
-            // tensor cores: many streams sharing the filter, or ONE long stream (its row is time-split over the tile rows;
-            // short calls of a single stream fall back to the CUDA-core FIR at run time, so that op carries both tap images)
+            // tensor cores: many streams sharing the filter, or a FEW long streams (each row is time-split over the tile rows;
+            // short calls of fewer than 8 streams fall back to the CUDA-core FIR at run time, so that op carries both tap images)
             const bool tensor = !(d->flags & SFE_FLAG_NO_TENSOR) && fmt == SFE_IN_I16 && step / s.up == 8 &&
-                                (d->n_streams >= 8 || d->n_streams == 1) && (int)g.size() <= toeplitz_max_taps();
-            const bool both = tensor && d->n_streams == 1;
+                                (int)g.size() <= toeplitz_max_taps();
+            const bool both = tensor && d->n_streams < 8;
             if (both) ok = ok && make_decim(op, g, (int)(step / s.up));
             if (tensor && make_toep(op, g)) {
                 c->plan += both ? "[toeplitz_i8_tcgen05 time-split | decim_fir for short calls]" : "[toeplitz_i8_tcgen05]";

@@ -41,6 +41,12 @@ namespace sfe {
 
 namespace {
 
+#ifndef SFE_TOEP_EARLY_RELEASE
+#define SFE_TOEP_EARLY_RELEASE 0
+#endif
+#ifndef SFE_TOEP_WAIT_NS
+#define SFE_TOEP_WAIT_NS 0           // suspend-time hint of mbarrier.try_wait: a waiting warp sleeps instead of spinning through issue slots
+#endif
 constexpr int TD = 8;              // decimation
 constexpr int TNO = 128 / TD;      // outputs per tile step and row
 constexpr int TNT = 3;             // tap digits
@@ -66,8 +72,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
     uint32_t done = 0;
     while (!done)
+#if SFE_TOEP_WAIT_NS
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n selp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity), "r"(SFE_TOEP_WAIT_NS) : "memory");
+#else
         asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
                      : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+#endif
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
 {
@@ -217,6 +228,13 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                     for (int q = 0; q < 4; q++)
                         asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
                                      : "=r"(v[q].x), "=r"(v[q].y), "=r"(v[q].z), "=r"(v[q].w) : "r"(sa + q * 4096));
+                    // release the slot BEFORE waiting for room in the operand ring, so that the TMA runs ahead of the MMA
+                    // instead of in step with it (the arrive has release semantics: this thread's loads above are ordered
+                    // before it, and the issuer puts a proxy fence between its acquire and the refill)
+#if SFE_TOEP_EARLY_RELEASE
+                    mbar_arrive(&bar_st_empty[q_slot]);
+                    if (++q_slot == Q) { q_slot = 0; q_par ^= 1; }
+#endif
                 } else {
                     const long n0 = X0 + 128 * m + 4 * lane;
 #pragma unroll
@@ -247,10 +265,12 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&bar_full[slot]);
-                if (staged(m)) {                           // the staged rows are in registers (and split): the slot may be refilled
+#if !SFE_TOEP_EARLY_RELEASE
+                if (staged(m)) {                           // the staged rows are split and stored: the slot may be refilled
                     mbar_arrive(&bar_st_empty[q_slot]);
                     if (++q_slot == Q) { q_slot = 0; q_par ^= 1; }
                 }
+#endif
             }
         }
     } else if (warp == W_MMA) {
@@ -435,7 +455,19 @@ int launch_toeplitz(const ToepParams &p, cudaStream_t st)
     static const bool no_split = getenv("SFE_TOEP_NO_SPLIT") != nullptr;   // tuning hook
     const long Kp = 1024, Q = TD * Kp, B = 128L * p.KB;
     const long P = p.n_out / Kp;
-    if (p.n_streams != 1 || no_split || P < 4 || p.in.fmt != SFE_IN_I16) return launch_toeplitz_rows(p, st);
+    if (p.n_streams >= 8 || no_split || P < 4 || p.in.fmt != SFE_IN_I16) return launch_toeplitz_rows(p, st);
+    if (p.n_streams > 1) {                   // 2 ... 7 long streams: each one split on its own (rows of different streams are not one pitch apart)
+        for (int s = 0; s < p.n_streams; s++) {
+            ToepParams one = p;
+            one.n_streams = 1;
+            one.in.cur = static_cast<const uint32_t *>(p.in.cur) + (long)s * p.in.pitch;
+            one.in.hist = static_cast<const uint32_t *>(p.in.hist) + (long)s * p.in.H;
+            one.out = p.out + (long)s * p.out_pitch;
+            const int rc1 = launch_toeplitz(one, st);
+            if (rc1 != SFE_OK) return rc1;
+        }
+        return SFE_OK;
+    }
     ToepParams a = p;                        // piece 0: the real history
     a.n_out = Kp;
     int rc = launch_toeplitz_rows(a, st);

@@ -330,18 +330,19 @@ def test_box_device_resident(gpu_lib, oracle_lib):
 
 # ---- one long stream on the tensor cores: the row is time-split over the tile rows -----------------------------------------
 
-@pytest.mark.parametrize("name,N,cut", [("cfg2", 1_000_003, 700_001), ("cfg2", 300_000, 299_000), ("cfg5", 400_001, 123_457)])
-def test_single_stream_tensor_time_split(gpu_lib, oracle_lib, name, N, cut):
+@pytest.mark.parametrize("name,S,N,cut", [("cfg2", 1, 1_000_003, 700_001), ("cfg2", 1, 300_000, 299_000), ("cfg5", 1, 400_001, 123_457),
+                                          ("cfg2", 3, 500_003, 300_008), ("cfg5", 7, 200_000, 150_001)])
+def test_single_stream_tensor_time_split(gpu_lib, oracle_lib, name, S, N, cut):
     """cfg 2 as BASELINE.json words it is ONE channel: its decimate-by-8 FIR runs on the tcgen05 kernel with the row cut
     into pieces that become tile rows (long calls), and on the CUDA-core FIR for short calls; two ragged calls so that
     history, a long and a short call and the seam between the two plans are all exercised"""
     from oracle import oracle as O
     flags = 8 if name == "cfg5" else 0            # cfg 5 without the bank plan: fused blkconv*decimate on the tensor cores
-    cfg = dict(F.CONFIGS[name], S=1, N=N)
+    cfg = dict(F.CONFIGS[name], S=S, N=N)       # 1 ... 7 streams: fewer than the 8 the many-stream tile launch wants
     iq = F.make_input(cfg)
     iq[0, :200] = 32767
-    iq[0, 200:400] = -32768
-    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib)
+    iq[-1, 200:400] = -32768
+    ref, _ = O.chain_run(iq, cfg["in_fmt"], cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=4)
     ch = _chain(cfg, flags)
     assert "toeplitz_i8_tcgen05" in ch.plan, ch.plan
     got = np.concatenate([ch.process(iq[:, :cut]), ch.process(iq[:, cut:])], axis=1)
