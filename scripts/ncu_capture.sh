@@ -7,6 +7,8 @@ python bench.py "$@" --no-cpu --no-e2e --no-parity --steps 3 > gpurun_out/${tag}
 ncu --set full --clock-control none --import-source on -k regex:$rx -s $skip -c 1 -f -o gpurun_out/$tag \
     python bench.py "$@" --no-cpu --no-e2e --no-parity --steps 3 > gpurun_out/${tag}_ncu.log 2>&1
 python scripts/ncu_summary.py gpurun_out/$tag.ncu-rep > gpurun_out/${tag}_summary.json 2>/dev/null
+# gpurun copies at most 64 MiB back: the report itself (3-10 MB) is kept only on request (KEEP_REP=1)
+[ "${KEEP_REP:-0}" = 1 ] || rm -f gpurun_out/$tag.ncu-rep
 python - <<PY
 import json
 d=json.load(open("gpurun_out/${tag}_summary.json"))
