@@ -81,6 +81,11 @@ struct Ctx {
     bool out_interior;   // all N - ov outputs of the block are valid
     const void *in_base; // sample blk0 - ov of this stream's current row (interior blocks)
     void *out_base;      // output sample blk0 of this stream
+    // Pass 0 lets thread t work on column (t + rot) mod S instead of column t, so that every warp's 32 consecutive samples
+    // start on a 128-byte line of the row: a block starts wherever hop * block index puts it (3842 samples), and a warp
+    // access that straddles one more line than it has to costs the LSU data pipe -- this kernel's busiest unit -- one more
+    // wavefront per load and per store (3 instead of 2 for complex64, 2 instead of 1 for int16).
+    int rot_in, rot_out;
 };
 
 template <int KF> struct RawOf { typedef uint32_t type; };
@@ -166,7 +171,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
 #pragma unroll
     for (int u = 0; u < NB; u++) {
         const int beta = t + u * PL::TPF;
-        const int b = (beta / S) * M, j = beta % S;
+        const int b = (beta / S) * M, j = P == 0 ? ((beta + c.rot_in) & (S - 1)) : beta % S;
         const int pb = phi(b + j);
         float2 v[R];
         if (P == 0) {
@@ -208,7 +213,7 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
 #pragma unroll
     for (int u = 0; u < NB; u++) {
         const int beta = t + u * PL::TPF;
-        const int b = (beta / S) * M, j = beta % S;
+        const int b = (beta / S) * M, j = P == 0 ? ((beta + c.rot_out) & (S - 1)) : beta % S;
         const int pb = phi(b + j);
         float2 v[R];
         float2 w[16];
@@ -262,7 +267,7 @@ __global__ void __launch_bounds__(Plan<N>::TPF *FPB, MINB) blkconv_fft_kernel(co
     const int f = threadIdx.x / PL::TPF, t = threadIdx.x % PL::TPF;
     const long id = (long)blockIdx.x * FPB + f;
     const long total = (long)p.n_streams * p.n_blocks;
-    Ctx c{p, 0, 0, id < total, false, false, nullptr, nullptr};
+    Ctx c{p, 0, 0, id < total, false, false, nullptr, nullptr, 0, 0};
     if (c.active) {
         c.stream = (int)(id / p.n_blocks);
         c.blk0 = (id % p.n_blocks) * (long)p.hop;
@@ -272,6 +277,9 @@ __global__ void __launch_bounds__(Plan<N>::TPF *FPB, MINB) blkconv_fft_kernel(co
         constexpr int EB = KF == KF_I16 ? 4 : KF == KF_U8 ? 2 : KF == KF_C64 ? 8 : 4;
         c.in_base = static_cast<const char *>(p.in.cur) + ((long)c.stream * p.in.pitch + first) * EB;
         c.out_base = static_cast<char *>(p.out) + ((long)c.stream * p.out_pitch + c.blk0) * (KF == KF_REAL ? 4 : 8);
+        constexpr int OB = KF == KF_REAL ? 4 : 8;
+        c.rot_in = (int)(((128u - (unsigned)(reinterpret_cast<uintptr_t>(c.in_base) & 127u)) & 127u) / EB);
+        c.rot_out = (int)(((128u - (unsigned)((reinterpret_cast<uintptr_t>(c.out_base) - (uintptr_t)p.ov * OB) & 127u)) & 127u) / OB);
     }
     float2 *X = smem + f * PL::PADN;
     float2 keep[16];
