@@ -270,34 +270,35 @@ __device__ __forceinline__ void split_pos(const BankParams &p, long k, long &M, 
 }
 
 // ceil(a / b) for b > 0 and any sign of a
-__host__ __device__ __forceinline__ long cdiv_l(long a, long b) { return a >= 0 ? (a + b - 1) / b : -((-a) / b); }
+template <class T> __host__ __device__ __forceinline__ T cdiv_t(T a, T b) { return a >= 0 ? (a + b - 1) / b : -((-a) / b); }
 
 // first output index k in [0, n_out] whose newest sample, counted from sample -H, is >= X
-// (rh_k = n_first + D floor(pos_k / L) + H with pos_k = pos0 + k step: monotonic in k)
-__host__ __device__ __forceinline__ long bank_first_k(const BankParams &p, long X)
+// (rh_k = n_first + D floor(pos_k / L) + H with pos_k = pos0 + k step: monotonic in k).  T = int when the host has
+// checked that every position of the call fits 31 bits (p.fits32): 64-bit division is a software routine of ~80
+// instructions, and every warp does seven of them before it can issue its first load.
+template <class T> __host__ __device__ __forceinline__ long bank_first_k(const BankParams &p, long X)
 {
-    const long Mmin = cdiv_l(X - p.n_first - p.H, p.D);
-    long k = cdiv_l((long)p.L * Mmin - p.pos0, p.step);
+    const T Mmin = cdiv_t<T>((T)(X - p.n_first - p.H), (T)p.D);
+    T k = cdiv_t<T>((T)p.L * Mmin - (T)p.pos0, (T)p.step);
     if (k < 0) k = 0;
-    if (k > p.n_out) k = p.n_out;
-    return k;
+    if (k > (T)p.n_out) k = (T)p.n_out;
+    return (long)k;
 }
 
 // ring slots [lo, hi) (SB boxes each, absolute box grid from sample -H) that hold every window of the call
 struct BankSpan {
     int lo, hi;
 };
-template <int SPC, int SB>
-__host__ __device__ __forceinline__ BankSpan bank_span(const BankParams &p)
+template <int SPC, int SB, class T> __host__ __device__ __forceinline__ BankSpan bank_span(const BankParams &p)
 {
-    long pos = p.pos0, M = pos / p.L;
-    if (pos - M * p.L < 0) M -= 1;
-    const long rh0 = p.n_first + (long)p.D * M + p.H;
-    pos = p.pos0 + (p.n_out - 1) * p.step;
-    M = pos / p.L;
-    if (pos - M * p.L < 0) M -= 1;
-    const long rh1 = p.n_first + (long)p.D * M + p.H;
-    const long q0 = rh0 / SPC - p.nc + 1, q1 = rh1 / SPC;             // first and last chunk read
+    T pos = (T)p.pos0, M = pos / (T)p.L;
+    if (pos - M * (T)p.L < 0) M -= 1;
+    const T rh0 = (T)p.n_first + (T)p.D * M + (T)p.H;
+    pos = (T)p.pos0 + (T)(p.n_out - 1) * (T)p.step;
+    M = pos / (T)p.L;
+    if (pos - M * (T)p.L < 0) M -= 1;
+    const T rh1 = (T)p.n_first + (T)p.D * M + (T)p.H;
+    const T q0 = rh0 / SPC - p.nc + 1, q1 = rh1 / SPC;             // first and last chunk read
     BankSpan s;
     s.lo = (int)((q0 >> 3) / SB);
     s.hi = (int)((q1 >> 3) / SB) + 1;
@@ -341,26 +342,31 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     // ---- state carry, folded into this kernel: hist_new[s] <- the last H samples of (hist_old[s] ++ cur[s][0..n)) ----
     // A few elements per thread, spread over the whole grid; it needs nothing this kernel computes and writes a buffer
     // this kernel never reads, so a call is ONE launch (the separate save_tail kernel remains for calls without outputs).
-    if (p.hist_new != nullptr) {
-        asm volatile("griddepcontrol.wait;" ::: "memory");           // the buffer was the previous call's hist_old
-        const long total = (long)p.n_streams * p.H;
-        const long stride = (long)gridDim.x * (WARPS * 32);
+    // Every thread runs it once: behind its warp's first TMA issues (the copies' latency then overlaps the boxes' flight),
+    // or on its way out when the warp has no work item.
+    auto carry = [&]() {
+        asm volatile("griddepcontrol.wait;" ::: "memory");           // (a no-op once passed) the target was the previous call's hist_old
+        if (p.hist_new == nullptr) return;
+        const unsigned total = (unsigned)p.n_streams * (unsigned)p.H, stride = gridDim.x * (WARPS * 32), H = (unsigned)p.H;   // (checked on the host: fits)
+        const long n_h = p.in.n - p.H;
         if (conv_spc(CONV) == 4) {
             const uint32_t *cur = static_cast<const uint32_t *>(p.in.cur), *ho = static_cast<const uint32_t *>(p.in.hist);
             uint32_t *hn = static_cast<uint32_t *>(p.hist_new);
-            for (long e = (long)blockIdx.x * (WARPS * 32) + threadIdx.x; e < total; e += stride) {
-                const long srow = e / p.H, i = e - srow * p.H, src = p.in.n + i - p.H;
-                hn[e] = src >= 0 ? __ldg(cur + srow * p.in.pitch + src) : __ldg(ho + srow * p.H + (p.H + src));
+            for (unsigned e = blockIdx.x * (WARPS * 32) + threadIdx.x; e < total; e += stride) {
+                const unsigned srow = e / H, i = e - srow * H;
+                const long src = n_h + i;
+                hn[e] = src >= 0 ? __ldg(cur + (long)srow * p.in.pitch + src) : __ldg(ho + (long)srow * p.H + (p.H + src));
             }
         } else {
             const uint16_t *cur = static_cast<const uint16_t *>(p.in.cur), *ho = static_cast<const uint16_t *>(p.in.hist);
             uint16_t *hn = static_cast<uint16_t *>(p.hist_new);
-            for (long e = (long)blockIdx.x * (WARPS * 32) + threadIdx.x; e < total; e += stride) {
-                const long srow = e / p.H, i = e - srow * p.H, src = p.in.n + i - p.H;
-                hn[e] = src >= 0 ? __ldg(cur + srow * p.in.pitch + src) : __ldg(ho + srow * p.H + (p.H + src));
+            for (unsigned e = blockIdx.x * (WARPS * 32) + threadIdx.x; e < total; e += stride) {
+                const unsigned srow = e / H, i = e - srow * H;
+                const long src = n_h + i;
+                hn[e] = src >= 0 ? __ldg(cur + (long)srow * p.in.pitch + src) : __ldg(ho + (long)srow * p.H + (p.H + src));
             }
         }
-    }
+    };
 
     // ---- this warp's work item ---------------------------------------------------------------------------
     // An item is a group of 32 streams and a contiguous range of BOXES (32-sample time blocks), not of outputs: every
@@ -371,21 +377,21 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
     // 15 % at 128 (the per-GPU shard of the 8-GPU split), where an item is only 17 outputs long.
     // (a warp without work still waits for the table copy: a CTA must not retire with a bulk copy into its shared memory in flight)
     const long item = (long)blockIdx.x * WARPS + warp;
-    if (item >= (long)p.n_groups * p.n_seg) { mbar_wait(tbar, 0); return; }
+    if (item >= (long)p.n_groups * p.n_seg) { carry(); mbar_wait(tbar, 0); return; }
     const int g = (int)(item % p.n_groups), seg = (int)(item / p.n_groups);
     constexpr int SPC = conv_spc(CONV);             // samples per 16-byte chunk
     const int NC = p.nc;
     const int row_bytes = p.row_len * 4;
 
-    const BankSpan sp = bank_span<SPC, SB>(p);      // slots [sp.lo, sp.hi) hold every window of the call
+    const BankSpan sp = p.fits32 ? bank_span<SPC, SB, int>(p) : bank_span<SPC, SB, long>(p);   // slots [sp.lo, sp.hi) hold every window of the call
     const int sA = sp.lo + (int)((long)(sp.hi - sp.lo) * seg / p.n_seg), sB = sp.lo + (int)((long)(sp.hi - sp.lo) * (seg + 1) / p.n_seg);
-    if (sA >= sB) { mbar_wait(tbar, 0); return; }
+    if (sA >= sB) { carry(); mbar_wait(tbar, 0); return; }
     const int box0 = sA * SB, box_end = sB * SB, n_boxes = box_end - box0;
     // outputs this item touches: [k_lo, k_end) -- the first window that ends at or behind box0, up to the first window that
     // opens at or behind box_end; the first n_inh of them opened before box0 (inherited from the item before)
-    const long k_lo = bank_first_k(p, (long)SPC * 8 * box0);
-    const long k_end = bank_first_k(p, (long)SPC * (8L * box_end + NC - 1));
-    if (k_lo >= k_end) { mbar_wait(tbar, 0); return; }   // no window meets these boxes (cannot happen between two outputs of a call)
+    const long k_lo = p.fits32 ? bank_first_k<int>(p, (long)SPC * 8 * box0) : bank_first_k<long>(p, (long)SPC * 8 * box0);
+    const long k_end = p.fits32 ? bank_first_k<int>(p, (long)SPC * (8L * box_end + NC - 1)) : bank_first_k<long>(p, (long)SPC * (8L * box_end + NC - 1));
+    if (k_lo >= k_end) { carry(); mbar_wait(tbar, 0); return; }   // no window meets these boxes (cannot happen between two outputs of a call)
 
     long M_next;
     int ph_next;
@@ -420,17 +426,14 @@ fused_bank_kernel(const __grid_constant__ CUtensorMap map_cur, const __grid_cons
             }
         }
     };
-    // This grid may have been launched as a programmatic dependent of the state carry of the previous call on the stream
-    // (launch_bank_rows): everything above -- barriers, the table copy, the index arithmetic -- then ran beside that
-    // call's last CTAs.  From here on the kernel reads what earlier work on the stream produced (history, samples) and
-    // writes what it may still be reading or writing (outputs, seam buffers): wait for it.  p.early_cur (tuning hook,
-    // SFE_BANK_EARLY_READ): rows of the caller's sample buffer are fetched before the wait, which is only correct when
-    // no kernel that precedes this call on the stream triggers its dependents before its last write to that buffer.
-    const bool early = p.early_cur && SB * slot0 >= hist_boxes;
-    if (!early) asm volatile("griddepcontrol.wait;" ::: "memory");
+    // (This grid may have been launched as a programmatic dependent of the previous call's kernel, launch_bank_rows: the
+    // barriers and the table copy above then ran beside that call's last CTAs; griddepcontrol.wait above restored the
+    // stream order before anything earlier work produced is read -- history, samples -- or anything it may still use is
+    // written -- outputs, seam buffers, the new history.)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (lane == 0)
         for (int b = 0; b < NST && b < n_slots; b++) issue(slot0 + b, b);
-    if (early) asm volatile("griddepcontrol.wait;" ::: "memory");
+    carry();
     // The next call's grid may start its prologue as soon as every CTA of this one has got here (it then waits, as this
     // one just did, for this grid to complete before it reads or writes anything this grid touches).
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -873,7 +876,7 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
     p.n_groups = (p.n_streams + BOX_ROWS - 1) / BOX_ROWS;
     // One work item per warp slot of the machine (rounded down: one item too many would cost a whole second wave).  Items
     // are ranges of ring slots; a window may straddle ONE seam between items, so an item is at least a window long.
-    const BankSpan sp = spc == 4 ? (v.sb == 2 ? bank_span<4, 2>(p) : bank_span<4, 1>(p)) : (v.sb == 2 ? bank_span<8, 2>(p) : bank_span<8, 1>(p));
+    const BankSpan sp = spc == 4 ? (v.sb == 2 ? bank_span<4, 2, long>(p) : bank_span<4, 1, long>(p)) : (v.sb == 2 ? bank_span<8, 2, long>(p) : bank_span<8, 1, long>(p));
     const long span_slots = sp.hi - sp.lo;
     const long win_boxes = ((p.nc + 7) >> 3) + 1;
     const long min_slots = (win_boxes + v.sb - 1) / v.sb + 1;
@@ -898,8 +901,11 @@ static int launch_bank_rows(const BankParams &p_in, cudaStream_t st)
     // their prologue early; griddepcontrol.wait in the kernel restores the stream order before any dependent access.
     // Behind anything else (a copy, a kernel that never triggers) the launch is an ordinary one.
     static const bool no_pdl = getenv("SFE_NO_PDL") != nullptr;
-    static const bool early_read = getenv("SFE_BANK_EARLY_READ") != nullptr;
-    p.early_cur = early_read && !no_pdl ? 1 : 0;
+    {   // every position of the call in 31 bits: the kernel's index arithmetic then uses 32-bit division
+        const double top = (double)p.pos0 + (double)p.n_out * (double)p.step + (double)p.L;
+        const double rh = (double)p.n_first + (double)p.D * (top / p.L + 1) + p.H + 64.0 * p.nc;
+        p.fits32 = (top < 2.0e9 && rh * 8 < 2.0e9 && (double)p.L * (rh / p.D + 2) < 2.0e9 && p.pos0 > -2.0e9) ? 1 : 0;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((items + v.warps - 1) / v.warps));
     cfg.blockDim = dim3(v.warps * 32);

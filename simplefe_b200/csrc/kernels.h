@@ -108,7 +108,7 @@ struct BankParams {
     int n_groups, n_seg;
     float2 *parts;        // seam exchange: two parts of every output whose window straddles two work items
     int *seam_cnt;        // arrivals per seam (zero between launches)
-    int early_cur;        // tuning hook: fetch rows of `in.cur` before griddepcontrol.wait
+    int fits32;           // every position of the call fits 31 bits: 32-bit index arithmetic in the kernel
     void *hist_new;       // not null: the kernel also performs the state carry (last H samples of hist ++ cur) into this buffer
 };
 int bank_nc(int Tc, int spc);         // 16-byte chunks (spc samples each) of taps for a composite filter of Tc taps
