@@ -128,6 +128,9 @@ template <int KF> __device__ __forceinline__ void store_output(const Ctx &c, int
 // the other eleven are products of those, at most three multiplications deep (relative error < 3e-7, two orders inside
 // the parity budget).  With fifteen loads per thread and pass the twiddle rows were 18 % of this kernel's LSU
 // wavefronts, and the LSU data pipe is what bounds it (profiles/r02_ncu_k1_c64_before.json: 79.5 % of peak).
+#ifndef SFE_FFT_PACKED_TWMUL
+#define SFE_FFT_PACKED_TWMUL 0     // data x twiddle as FMUL2 + FFMA2 instead of four scalar instructions (tuning switch)
+#endif
 #ifndef SFE_FFT_TW_PRODUCTS
 #define SFE_FFT_TW_PRODUCTS 1
 #endif
@@ -197,7 +200,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
         for (int sl = 0; sl < R; sl++) {
             const int q = brev<R>(sl);
             float2 y = v[sl];
-            if (S > 1 && q != 0) y = cmul(y, w[q & 15]);
+            if (S > 1 && q != 0) y = SFE_FFT_PACKED_TWMUL ? cmul_pk(y, w[q & 15]) : cmul(y, w[q & 15]);
             if (KEEP) keep[u * R + q] = y;
             else X[phi_at<S>(pb, b + j, q)] = y;
         }
@@ -221,7 +224,7 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
 #pragma unroll
         for (int q = 0; q < R; q++) {
             float2 y = FROMREG ? keep[u * R + q] : X[phi_at<S>(pb, b + j, q)];
-            if (S > 1 && q != 0) y = cmul_conj(y, w[q & 15]);
+            if (S > 1 && q != 0) y = SFE_FFT_PACKED_TWMUL ? cmul_pk(y, make_float2(w[q & 15].x, -w[q & 15].y)) : cmul_conj(y, w[q & 15]);
             v[q] = y;
         }
         if (SFE_FFT_PACKED) dft_dif_packed<R, +1>(v);
