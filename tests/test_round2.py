@@ -353,3 +353,41 @@ def test_single_stream_tensor_time_split(gpu_lib, oracle_lib, name, S, N, cut):
     alt = _chain(cfg, flags | 4)
     alt_y = np.concatenate([alt.process(iq[:, :cut]), alt.process(iq[:, cut:])], axis=1)
     assert np.max(np.abs(got - alt_y)) <= 1e-5 * np.max(np.abs(ref))
+
+
+# ---- K3 seam exchange: random launch shapes, run twice (a race would show as run-to-run differences) ----------------------
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_bank_seam_exchange_random_shapes(gpu_lib, oracle_lib, seed):
+    """K3's work items are box ranges; a window that straddles two items is summed by whichever warp arrives second
+    (parts in global memory, an arrival counter per seam).  Random stream counts (1 ... 300: 1 ... 10 row groups, so
+    2 ... 1184 items per group), lengths, input formats and two-call splits: every shape twice from a fresh chain --
+    bit-identical results (the summation order is fixed: older + newer) -- against the staged plan of the same chain on
+    every row and against the reference classes on a few rows."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(1000 + seed)
+    for _ in range(12):
+        base = ["cfg5", "cfg3"][int(rng.integers(0, 2))]
+        fmt = [F.IN_I16, F.IN_U8][int(rng.integers(0, 2))]
+        S = int(rng.choice([1, 2, 31, 32, 33, 64, 100, 257, 300]))
+        N = int(rng.integers(6_000, 400_000 if S <= 64 else 120_000))
+        cut = int(rng.integers(1, N))
+        cfg = dict(F.CONFIGS[base], S=S, N=N, in_fmt=fmt, seed=int(rng.integers(0, 10 ** 6)))
+        one = F.make_input(dict(cfg, S=min(S, 8)))
+        iq = np.ascontiguousarray(np.stack([np.roll(one[s % len(one)], 17 * s, axis=0) for s in range(S)]))
+        runs = []
+        for rep in range(2):
+            ch = _chain(cfg)
+            assert ch.plan.startswith("bank_fused"), ch.plan
+            runs.append(np.concatenate([ch.process(iq[:, :cut]), ch.process(iq[:, cut:])], axis=1))
+        assert np.array_equal(runs[0], runs[1]), (base, fmt, S, N, cut, "run-to-run difference")
+        alt_ch = _chain(cfg, flags=8)
+        alt = np.concatenate([alt_ch.process(iq[:, :cut]), alt_ch.process(iq[:, cut:])], axis=1)
+        assert alt.shape == runs[0].shape, (base, fmt, S, N, cut, alt.shape, runs[0].shape)
+        scale = float(np.max(np.abs(alt))) or 1.0
+        assert float(np.max(np.abs(runs[0] - alt))) <= 2e-5 * scale, (base, fmt, S, N, cut)
+        rows = sorted({0, S // 2, S - 1})
+        ref, _ = O.chain_run(iq[rows], fmt, cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=3)
+        for k, s in enumerate(rows):
+            nrms, peak = F.err_metrics(runs[0][s], ref[k])
+            assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (base, fmt, S, N, cut, s, nrms, peak)
