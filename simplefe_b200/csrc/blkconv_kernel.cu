@@ -232,7 +232,8 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
 #pragma unroll
         for (int sl = 0; sl < R; sl++) {
             const int k = brev<R>(sl);
-            if (P == 0) store_output<KF>(c, b + j + k * S, v[sl]);
+            // (interpolating epilogue: the time-domain block goes back into the slots this thread has just read)
+            if (P == 0 && c.p.lerp_sched == nullptr) store_output<KF>(c, b + j + k * S, v[sl]);
             else X[phi_at<S>(pb, b + j, k)] = v[sl];
         }
     }
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(Plan<N>::TPF *FPB, MINB) blkconv_fft_kernel(co
     Ctx c{p, 0, 0, id < total, false, false, nullptr, nullptr, 0, 0};
     if (c.active) {
         c.stream = (int)(id / p.n_blocks);
-        c.blk0 = (id % p.n_blocks) * (long)p.hop;
+        c.blk0 = p.blk_start + (id % p.n_blocks) * (long)p.hop;
         const long first = c.blk0 - p.ov;
         c.in_interior = first >= 0 && first + N <= p.in.n;
         c.out_interior = c.blk0 + (N - p.ov) <= p.in.n;
@@ -312,6 +313,24 @@ __global__ void __launch_bounds__(Plan<N>::TPF *FPB, MINB) blkconv_fft_kernel(co
             keep[u * RL + q] = cmul(keep[u * RL + q], __ldg(p.hp + (u * RL + q) * PL::TPF + t));
 
     InvChain<N, PL::NP - 1, KF>::run(X, t, c, keep);
+
+    if (p.lerp_sched != nullptr) {
+        // X[phi(i)] now holds s[blk0 - ov + i]; valid for i >= ov.  The schedule is the same for every stream.
+        __syncthreads();
+        if (c.active) {
+            const long blk = id % p.n_blocks;
+            const int k_lo = __ldg(p.lerp_kidx + blk), k_hi = __ldg(p.lerp_kidx + blk + 1);
+            const long org = c.blk0 - p.ov;
+            float2 *orow = reinterpret_cast<float2 *>(p.out) + (long)c.stream * p.out_pitch;
+            for (int k = k_lo + t; k < k_hi; k += PL::TPF) {
+                const int2 e = __ldg(reinterpret_cast<const int2 *>(p.lerp_sched) + k);   // {pos, mu}
+                const int i = (int)((long)e.x - org);
+                const float2 a = X[phi(i)], b2 = X[phi(i + 1)];
+                const float w1 = __int_as_float(e.y), w0 = 1.0f - w1;
+                orow[k] = make_float2(fmaf(w1, b2.x, w0 * a.x), fmaf(w1, b2.y, w0 * a.y));
+            }
+        }
+    }
 }
 
 template <int N> int launch_n(const BlkconvParams &p, cudaStream_t st)
@@ -322,7 +341,9 @@ template <int N> int launch_n(const BlkconvParams &p, cudaStream_t st)
     if (total <= 0) return SFE_OK;
     const size_t smem = sizeof(float2) * PL::PADN * FPB;
     // resident CTAs per SM the register allocation must allow (SFE_K1_THREADS)
-    constexpr int MINB = PL::TPF * FPB <= 256 ? SFE_K1_THREADS / (PL::TPF * FPB) : 1;
+    // (1024 threads only where it was measured to pay and fits 64 registers without spills: N >= 2048; the two-FFT CTAs of the
+    // smaller sizes keep 768)
+    constexpr int MINB = PL::TPF * FPB <= 256 ? (N >= 2048 ? SFE_K1_THREADS : 768) / (PL::TPF * FPB) : 1;
     void (*kern)(const BlkconvParams) =
         p.in_real ? blkconv_fft_kernel<N, FPB, MINB, KF_REAL>
                   : p.in.fmt == SFE_IN_I16 ? blkconv_fft_kernel<N, FPB, MINB, KF_I16>

@@ -79,6 +79,9 @@ struct Op {
     int row_len = 0, n_rows = 0, rows_per_phase = 1, nc = 0, n_live = 1;
     long n_first = 0;
     bool bad_sched = false;
+    bool lerp = false;             // OP_BLKCONV whose kernel also does the interpolation of the one-phase stage behind it
+    int *d_kidx = nullptr;         //   first schedule entry of every FFT block (launch_block_index)
+    size_t d_kidx_cap = 0;
     float lerp_tap = 0.f;          // OP_POLY with one tap and one phase: interpolation only (poly_lerp_kernel)
     bool direct_fir = false;       // OP_POLY standing in for blkconv: every sample is an output (pos = k, mu = 0)
     // per call
@@ -195,7 +198,7 @@ bool alloc_hist(Op &op, int S)
 
 long stage_max_out(const Op &op, long n)
 {
-    if (op.kind == OP_BLKCONV || op.direct_fir) return n;
+    if ((op.kind == OP_BLKCONV && !op.lerp) || op.direct_fir) return n;
     if (op.kind == OP_BANK) {
         if (op.has_pre) {
             const long calls = (n + op.pre_blk - 1) / op.pre_blk;
@@ -227,7 +230,12 @@ void plan_call(sfe_chain *c, long n_in)
     long n = n_in;
     for (Op &op : c->ops) {
         op.n_in = n;
-        if (op.kind == OP_BLKCONV) {
+        if (op.kind == OP_BLKCONV && op.lerp) {
+            op.use_runs = true;
+            op.n_out = (long)walk_batch_runs(op.ws, 1, op.blk, op.rate, n, op.runs);
+            op.sched.uniform = false;
+            op.sched.count = op.n_out;
+        } else if (op.kind == OP_BLKCONV) {
             op.n_out = n;
         } else if (op.kind == OP_BANK) {
             long na = n;
@@ -371,7 +379,12 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             p.out = dst;
             p.out_pitch = dst_pitch;
             p.n_streams = ns;
-            p.n_blocks = (op.n_in + op.hop - 1) / op.hop;
+            p.n_blocks = op.lerp ? (op.n_out > 0 ? (op.n_in - 1) / op.hop + 1 : 0) : (op.n_in + op.hop - 1) / op.hop;
+            if (op.lerp) {
+                p.blk_start = -1;
+                p.lerp_sched = op.d_sched;
+                p.lerp_kidx = op.d_kidx;
+            }
             p.hop = op.hop;
             p.ov = op.ov;
             p.tw = op.tw;
@@ -498,7 +511,7 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
 int upload_schedules(sfe_chain *c, cudaStream_t st)
 {
     for (Op &op : c->ops) {
-        if (op.kind != OP_POLY || op.sched.uniform || op.n_out == 0) continue;
+        if (!(op.kind == OP_POLY || (op.kind == OP_BLKCONV && op.lerp)) || op.sched.uniform || op.n_out == 0) continue;
         const size_t need = sizeof(SchedEntry) * (size_t)op.n_out;
         if (op.d_sched_cap < need) {
             if (op.d_sched) cudaFree(op.d_sched);
@@ -530,8 +543,20 @@ int upload_schedules(sfe_chain *c, cudaStream_t st)
             if (!SFE_CUDA(cudaMemcpyAsync(op.d_runs, op.h_runs, rb, cudaMemcpyHostToDevice, st)) ||
                 !SFE_CUDA(cudaEventRecord(op.h_sched_done, st)))
                 return SFE_ERR_CUDA;
-            const int rc = launch_expand_sched(op.d_runs, (int)nr, op.d_sched, st);
+            int rc = launch_expand_sched(op.d_runs, (int)nr, op.d_sched, st);
             if (rc != SFE_OK) return rc;
+            if (op.lerp) {                       // which entries fall into which FFT block of the convolver
+                const long nb = (op.n_in - 1) / op.hop + 1;
+                if (op.d_kidx_cap < (size_t)nb + 1) {
+                    cudaFree(op.d_kidx);
+                    op.d_kidx = nullptr;
+                    op.d_kidx_cap = 0;
+                    if (!SFE_CUDA(cudaMalloc(&op.d_kidx, sizeof(int) * 2 * ((size_t)nb + 1)))) return SFE_ERR_CUDA;
+                    op.d_kidx_cap = 2 * ((size_t)nb + 1);
+                }
+                rc = launch_block_index(op.d_sched, op.n_out, -1, op.hop, nb, op.d_kidx, st);
+                if (rc != SFE_OK) return rc;
+            }
             continue;
         }
         // straight from the vector the walk filled, once its storage is registered (plan_call keeps it from moving)
@@ -718,6 +743,19 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
             op.hp = chain_spectrum(dev, d->bc_taps, d->bc_ntaps, op.N, nullptr);
             ok = ok && op.tw && op.hp;
             op.name = "blkconv_fft" + std::to_string(op.N) + (lerp_fused ? "(blkconv*stage_a_fir)" : "");
+            static const bool no_epi = getenv("SFE_NO_LERP_EPILOGUE") != nullptr;   // tuning hook: separate interpolation kernel
+            if (lerp_fused && !no_epi) {
+                // the interpolation that is left of stage a runs in the convolver's epilogue, from its shared-memory block:
+                // the full-rate convolved stream is never written (blocks overlap by one more sample, for s[pos + 1], and
+                // start at -1, for an output held over from the previous call)
+                op.lerp = true;
+                op.hop = op.N - op.ov - 1;
+                op.H = op.ov + 1;
+                op.up = 1;
+                op.blk = d->a.blk;
+                op.rate = d->a.rate;
+                op.name += "+lerp_epilogue";
+            }
         } else {
             // taps longer than any compiled transform: direct FIR = one-phase polyphase stage with step 1
             op.kind = OP_POLY;
@@ -736,6 +774,7 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
     for (int which = 0; which < 2 && ok && staged; which++) {
         const sfe_stage_desc &s = which == 0 ? d->a : d->b;
         if (s.klass == SFE_KLASS_NONE) continue;
+        if (which == 0 && !c->ops.empty() && c->ops.back().lerp) continue;   // stage a lives in the convolver's epilogue
         Op op{};
         op.in_fmt = fmt;
         op.up = s.up;
@@ -819,6 +858,7 @@ extern "C" void sfe_chain_destroy(sfe_chain *c)
         cudaFree(op.d_bmat);
         cudaFree(op.d_sched);
         cudaFree(op.d_runs);
+        cudaFree(op.d_kidx);
         if (op.h_runs) cudaFreeHost(op.h_runs);
         if (op.reg_ptr) cudaHostUnregister(op.reg_ptr);
         if (op.h_sched) cudaFreeHost(op.h_sched);

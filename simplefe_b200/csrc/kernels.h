@@ -20,6 +20,13 @@ struct BlkconvParams {
     const float2 *hp;     // tap spectrum, kernel (digit-reversed) order, pre-scaled by 1/N
     int mode;
     float scale;          // spectrum mode: 1/N (blkconv.cxx:50)
+    // Interpolating epilogue (chain.cu: a one-phase fractional-rate stage behind blkconv): the block's convolved samples
+    // stay in shared memory and the kernel writes only out[k] = (1-mu_k) s[pos_k] + mu_k s[pos_k + 1] for the schedule
+    // entries k in [lerp_kidx[b], lerp_kidx[b+1]) whose pos lies in block b.  Blocks then start at blk_start + b*hop with
+    // hop = fft_len - ov - 1 (one sample of overlap more, for s[pos + 1]) and blk_start = -1 (a held-over output).
+    long blk_start;
+    const SchedEntry *lerp_sched;   // nullptr: plain convolution output
+    const int *lerp_kidx;           // n_blocks + 1 entries
 };
 int launch_blkconv(int fft_len, const BlkconvParams &p, cudaStream_t st);
 bool blkconv_twiddle_table(int fft_len, std::vector<float2> &host);
@@ -134,5 +141,7 @@ int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long
 int launch_pack_dac10(const float *in, long n, uint8_t *out, cudaStream_t st);
 // d_out[run.k0 + j] <- entry j of every run (schedule.h: SchedRun)
 int launch_expand_sched(const SchedRun *d_runs, int n_runs, SchedEntry *d_out, cudaStream_t st);
+// kidx[b] = first entry whose pos >= blk_start + b*hop, b = 0 .. n_blocks (entries sorted by pos)
+int launch_block_index(const SchedEntry *d_sched, long n_out, long blk_start, int hop, long n_blocks, int *d_kidx, cudaStream_t st);
 
 }  // namespace sfe

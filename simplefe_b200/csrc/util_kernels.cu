@@ -101,6 +101,28 @@ int launch_save_tail(void *hist_new, const void *hist_old, const void *cur, long
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }
 
+__global__ void block_index_kernel(const SchedEntry *sched, long n_out, long blk_start, int hop, long n_blocks, int *kidx)
+{
+    const long b = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > n_blocks) return;
+    const long target = blk_start + b * hop;
+    long lo = 0, hi = n_out;                  // lower bound: positions increase strictly along the schedule
+    while (lo < hi) {
+        const long mid = (lo + hi) >> 1;
+        if ((long)sched[mid].pos < target) lo = mid + 1;
+        else hi = mid;
+    }
+    kidx[b] = (int)lo;
+}
+
+int launch_block_index(const SchedEntry *d_sched, long n_out, long blk_start, int hop, long n_blocks, int *d_kidx, cudaStream_t st)
+{
+    if (n_blocks < 0) return SFE_OK;
+    block_index_kernel<<<(unsigned)((n_blocks + 1 + 127) / 128), 128, 0, st>>>(d_sched, n_out, blk_start, hop, n_blocks, d_kidx);
+    count_launch();
+    return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
+}
+
 int launch_expand_sched(const SchedRun *d_runs, int n_runs, SchedEntry *d_out, cudaStream_t st)
 {
     if (n_runs <= 0) return SFE_OK;
