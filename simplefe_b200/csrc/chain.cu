@@ -1023,7 +1023,8 @@ static int process_host_groups(sfe_chain *c, const void *h_in, long n_in, long i
     // stream groups of ~64 MiB input: H2D(g+1) overlaps kernels(g) overlaps D2H(g-1) on two CUDA streams
     const size_t row_in = (size_t)n_in * eb;
     const long dpitch = (n_in + 7) & ~7L;   // device staging rows start 16-byte aligned in every format (TMA)
-    int gs = (int)((64u << 20) / (row_in ? row_in : 1));
+    static const long group_mb = getenv("SFE_HOST_GROUP_MB") ? atol(getenv("SFE_HOST_GROUP_MB")) : 64;   // tuning hook
+    int gs = (int)(((size_t)(group_mb > 0 ? group_mb : 64) << 20) / (row_in ? row_in : 1));
     if (gs < 1) gs = 1;
     if (gs > c->S) gs = c->S;
     if (c->S >= 4 && gs > (c->S + 3) / 4) gs = (c->S + 3) / 4;  // at least 4 groups so that copies overlap
