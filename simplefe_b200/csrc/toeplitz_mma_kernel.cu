@@ -21,7 +21,7 @@
 //   warp  4    MMA issue  one thread; tcgen05.mma.cta_group::1.kind::i8, commits to mbarriers
 //   warp  5    TMA issue  one thread; the raw int16 IQ rows of a K-block (32 streams x 128 samples = 16 KB) as ONE
 //                         cp.async.bulk.tensor box into a staging ring, several K-blocks ahead
-//   warps 6-13 producers  128-bit shared-memory loads of the staged rows, byte-plane split with PRMT, stores into the
+//   warps 6-9  producers  (eight stream rows of every K-block each) 128-bit shared-memory loads of the staged rows, byte-plane split with PRMT, stores into the
 //                         K-major SWIZZLE_128B operand tiles of a second ring (no im2col copy: consecutive steps
 //                         reuse KB-1 of their KB K-block tiles).  Round 1 loaded the rows with LDG into registers: the
 //                         producers then spent 70 % of their 1650 warp instructions per step on 64-bit row addresses,
@@ -52,7 +52,14 @@ constexpr int TNO = 128 / TD;      // outputs per tile step and row
 constexpr int TNT = 3;             // tap digits
 constexpr int TNCOL = TNT * TNO;   // 48 accumulator columns
 constexpr int TILE_BYTES = 128 * 128;
-constexpr int N_EPI_WARPS = 4, N_PROD_WARPS = 8;
+#ifndef SFE_TOEP_PROD_WARPS
+#define SFE_TOEP_PROD_WARPS 4        // 4 warps of 8 stream rows each; 8 x 4 (round 1) and 2 x 16 measured slower
+#endif
+constexpr int N_EPI_WARPS = 4, N_PROD_WARPS = SFE_TOEP_PROD_WARPS;
+constexpr int RPW = 32 / N_PROD_WARPS;                    // stream rows of a K-block per producer warp
+constexpr uint32_t ROW_STEP = N_PROD_WARPS * 512u;        // bytes between a warp's consecutive rows: staged rows are 512 B, and
+                                                          // their four plane rows 4 x 128 B of the operand tile (multiple of 1024: same swizzle)
+static_assert(N_PROD_WARPS == 2 || N_PROD_WARPS == 4 || N_PROD_WARPS == 8, "producer warps");
 constexpr int W_MMA = N_EPI_WARPS, W_TMA = N_EPI_WARPS + 1, W_PROD0 = N_EPI_WARPS + 2;
 constexpr int N_THREADS = 32 * (N_EPI_WARPS + 2 + N_PROD_WARPS);
 constexpr int MAX_RING = 12, MAX_STAGE = 6;
@@ -213,21 +220,21 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
         uint32_t soff[4];                                  // swizzled byte offsets of this thread's four plane rows (q = 0)
 #pragma unroll
         for (int k = 0; k < 4; k++) soff[k] = swz(4 * pw + k, 4 * lane);
-        const uint32_t st_off = (uint32_t)pw * 512u + (uint32_t)lane * 16u;   // this lane's 4 samples of staged row pw (+ 8 q rows)
+        const uint32_t st_off = (uint32_t)pw * 512u + (uint32_t)lane * 16u;   // this lane's 4 samples of staged row pw (+ N_PROD_WARPS q rows)
         PieceIter it(p);
         Piece pc;
         while (it.next(pc)) {
             const int s_base = pc.g * 32;
             const long m_end = pc.j1 + KB - 1;
             for (long m = pc.j0; m < m_end; m++) {
-                uint4 v[4];
+                uint4 v[RPW];
                 if (staged(m)) {
                     mbar_wait(&bar_st_full[q_slot], q_par);
                     const uint32_t sa = stage_sa + (uint32_t)q_slot * TILE_BYTES + st_off;
 #pragma unroll
-                    for (int q = 0; q < 4; q++)
+                    for (int q = 0; q < RPW; q++)
                         asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                                     : "=r"(v[q].x), "=r"(v[q].y), "=r"(v[q].z), "=r"(v[q].w) : "r"(sa + q * 4096));
+                                     : "=r"(v[q].x), "=r"(v[q].y), "=r"(v[q].z), "=r"(v[q].w) : "r"(sa + q * ROW_STEP));
                     // release the slot BEFORE waiting for room in the operand ring, so that the TMA runs ahead of the MMA
                     // instead of in step with it (the arrive has release semantics: this thread's loads above are ordered
                     // before it, and the issuer puts a proxy fence between its acquire and the refill)
@@ -238,8 +245,8 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                 } else {
                     const long n0 = X0 + 128 * m + 4 * lane;
 #pragma unroll
-                    for (int q = 0; q < 4; q++) {
-                        const int s = s_base + pw + 8 * q;
+                    for (int q = 0; q < RPW; q++) {
+                        const int s = s_base + pw + N_PROD_WARPS * q;
                         v[q].x = load_i16(p, s, n0);
                         v[q].y = load_i16(p, s, n0 + 1);
                         v[q].z = load_i16(p, s, n0 + 2);
@@ -252,16 +259,17 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                 mbar_wait(&bar_empty[slot], par ^ 1);      // slot free (first pass falls through)
                 const uint32_t tile = ring_sa + (uint32_t)slot * TILE_BYTES;
 #pragma unroll
-                for (int q = 0; q < 4; q++) {
+                for (int q = 0; q < RPW; q++) {
                     const uint32_t t01 = __byte_perm(v[q].x, v[q].y, 0x5140), t23 = __byte_perm(v[q].z, v[q].w, 0x5140);
                     const uint32_t u01 = __byte_perm(v[q].x, v[q].y, 0x7362), u23 = __byte_perm(v[q].z, v[q].w, 0x7362);
                     const uint32_t il = __byte_perm(t01, t23, 0x5410), ih = __byte_perm(t01, t23, 0x7632) ^ 0x80808080u;
                     const uint32_t ql = __byte_perm(u01, u23, 0x5410), qh = __byte_perm(u01, u23, 0x7632) ^ 0x80808080u;
-                    // rows 4*(pw + 8q) + k: the swizzle term (row & 7) does not depend on q, tiles rows 32 apart are 4096 B apart
-                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[0] + q * 4096), "r"(il) : "memory");
-                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[1] + q * 4096), "r"(ih) : "memory");
-                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[2] + q * 4096), "r"(ql) : "memory");
-                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[3] + q * 4096), "r"(qh) : "memory");
+                    // rows 4*(pw + N_PROD_WARPS*q) + k: the swizzle term (row & 7) does not depend on q, and tile rows
+                    // 4*N_PROD_WARPS apart are ROW_STEP bytes apart
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[0] + q * ROW_STEP), "r"(il) : "memory");
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[1] + q * ROW_STEP), "r"(ih) : "memory");
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[2] + q * ROW_STEP), "r"(ql) : "memory");
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[3] + q * ROW_STEP), "r"(qh) : "memory");
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&bar_full[slot]);
@@ -435,7 +443,7 @@ static int launch_toeplitz_rows(const ToepParams &p_in, cudaStream_t st)
     if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
     const long F = (long)p.n_groups * p.n_steps;
     long grid = F / 4 > 0 ? F / 4 : 1;                    // at least ~4 steps per CTA
-    // two CTAs per SM when their rings fit (72 registers x 448 threads and 128 TMEM columns each): the second CTA's warps
+    // two CTAs per SM when their rings fit (320 threads, at most 102 registers each, and 128 TMEM columns each): the second CTA's warps
     // fill the issue slots the first one leaves while its producers, MMA thread and epilogue wait on each other
     static const bool one_cta = getenv("SFE_TOEP_ONE_CTA") != nullptr;   // tuning hook
     const int per_sm = (2 * (smem + 2048) <= 227 * 1024 && !one_cta) ? 2 : 1;
