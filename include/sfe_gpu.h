@@ -254,6 +254,29 @@ int sfe_tx_feed_callback(unsigned char *buffer, int length, void *feed);
 /* which: 0 underflows ("U"), 1 bytes delivered, 2 bytes waiting, 3 floats a write can take now */
 long sfe_tx_feed_stat(sfe_tx_feed *f, int which);
 
+/* ---- (7) a process() call that allocates nothing ---------------------------------------------------------------------- */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+   (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  One decimate / resample process() call
+   (the arithmetic of (1b)) on the calling thread's CURRENT CUDA device, with every buffer the caller's: device pointers for
+   the taps (n_taps floats as given to the reference constructor), the input (n_in floats), the output (room for
+   min(out_len, floor(n_in/rate) + 2) floats) and the history -- the last n_hist input samples BEFORE this call, normally the
+   tail of the previous call's input buffer; samples older than that read as zero, so a stream needs
+   n_hist >= (n_taps - 1) / upsample + 1 from its second call on, and NULL / 0 is a fresh object.  The three scalars a
+   reference object carries between calls (decimate.h:55-59) live in the caller's sfe_walk_state: zero it for a fresh
+   object; it is advanced on success and untouched on failure.  exact != 0 is sfe_polyphase_set_exact.
+   The call's schedule table is the only scratch memory, and it sits in a static device array inside the library
+   (8 bytes x SFE_NOALLOC_MAX_OUT = 2 MB on every GPU that loads libsfegpu, until exit): no cudaMalloc, cudaFree or
+   allocating library routine runs.  A call that would produce more than SFE_NOALLOC_MAX_OUT outputs is refused with
+   SFE_ERR_CAP (message in sfe_last_error; feed the stream in smaller calls).  All calls on a device share the array:
+   calls that overlap on the GPU (two streams, two host threads) race on it -- issue them on one stream, or serialise them.
+   Asynchronous on `stream` (0 = the legacy default stream).  Returns the number of outputs written, 0 after printing the
+   reference's message for its own argument checks, or a negative status. */
+#define SFE_NOALLOC_MAX_OUT (1 << 18)
+typedef struct sfe_walk_state { int pos; float mu; int held; } sfe_walk_state;
+int sfe_polyphase_process_noalloc(int klass, const float *d_taps, int n_taps, int upsample, sfe_walk_state *state,
+                                  const float *d_hist, int n_hist, const float *d_in, int n_in, float *d_out, int out_len,
+                                  float rate, int exact, void *stream);
+
 /* ---- sample format helpers (device wire formats) ---------------------- */
 /* float -> 10-bit DAC words, 4 samples -> 5 bytes: examples/bpsk/bpsk.cxx:76-101,
    gr-simplefe/lib/sink_c_impl.cc:118-144.  n must be a multiple of 4; device pointers. */

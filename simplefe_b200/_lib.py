@@ -17,6 +17,11 @@ class StageDesc(C.Structure):
                 ("blk", C.c_int), ("rate", C.c_float)]
 
 
+class WalkStateC(C.Structure):
+    """sfe_walk_state (include/sfe_gpu.h section 7): the scalars a decimate/resample object carries between calls"""
+    _fields_ = [("pos", C.c_int), ("mu", C.c_float), ("held", C.c_int)]
+
+
 class ChainDesc(C.Structure):
     _fields_ = [("in_fmt", C.c_int), ("n_streams", C.c_int), ("bc_taps", C.POINTER(C.c_float)),
                 ("bc_ntaps", C.c_int), ("bc_fft", C.c_int), ("a", StageDesc), ("b", StageDesc), ("flags", C.c_int)]
@@ -73,6 +78,7 @@ SYMBOLS = {
     "sfe_box_process_dev": (_ci, [_vp, C.POINTER(_vp), _cl, _cl, C.POINTER(_vp), _cl, C.POINTER(_cl), C.POINTER(_vp)]),
     "sfe_box_sync": (_ci, [_vp]),
     "sfe_pack_dac10_dev": (_ci, [_vp, _cl, _vp, _vp]),
+    "sfe_polyphase_process_noalloc": (_ci, [_ci, _vp, _ci, _ci, C.POINTER(WalkStateC), _vp, _ci, _vp, _ci, _vp, _ci, _cf, _ci, _vp]),
     "sfe_bpsk_tx_create": (_vp, [_f32p, _ci, _ci, _cf, _ci]),
     "sfe_bpsk_tx_destroy": (None, [_vp]),
     "sfe_bpsk_tx_reset": (_ci, [_vp]),

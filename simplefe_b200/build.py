@@ -14,7 +14,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libsfegpu.so")
 
-CU_SOURCES = ["capi.cu", "chain.cu", "blkconv_kernel.cu", "polyphase_kernel.cu", "util_kernels.cu", "toeplitz_mma_kernel.cu", "fused_bank_kernel.cu", "ring.cu", "bpsk_tx_kernel.cu", "bpsk_tx.cu", "feed.cu", "box.cu"]
+CU_SOURCES = ["capi.cu", "chain.cu", "blkconv_kernel.cu", "polyphase_kernel.cu", "util_kernels.cu", "toeplitz_mma_kernel.cu", "fused_bank_kernel.cu", "ring.cu", "bpsk_tx_kernel.cu", "bpsk_tx.cu", "feed.cu", "box.cu", "no_alloc.cu"]
 CPP_SOURCES = ["schedule.cpp"]
 HEADERS = ["kernels.h", "schedule.h", "sfe_common.cuh", "sfe_fft.cuh", "../../include/sfe_gpu.h"]
 
