@@ -24,6 +24,9 @@
 #ifndef SFE_K1_THREADS
 #define SFE_K1_THREADS 1024
 #endif
+#ifndef SFE_K1_ROWPAD
+#define SFE_K1_ROWPAD 1
+#endif
 #ifndef SFE_FFT_PACKED
 #define SFE_FFT_PACKED 1
 #endif
@@ -42,7 +45,14 @@ template <int N> struct Plan {
     static constexpr int LASTR = 1 << (LOGN % 4);          // 1 = none
     static constexpr int NP = FULL + (LASTR > 1 ? 1 : 0);  // passes
     static constexpr int TPF = N / 16;                     // threads per FFT
-    static constexpr int PADN = N + N / 16;                // padded shared-memory length
+    // Shared-memory layout.  General: one element of padding per 16 (stride-16 accesses of the last pass hit 16 banks).
+    // N = 16^3 (SFE_K1_ROWPAD): 16 rows of 256 with ONE element of padding per row, and the last pass takes its 16-element
+    // groups in transposed thread order (a half-warp then touches 16 different rows = 16 different banks).  Pass 0 lets
+    // thread t work on column (t + rot) mod 256 (Ctx::rot_in): with padding inside the rows a half-warp whose 16 columns do
+    // not start on a multiple of 16 straddles a padding slot and its first and last lane share a bank -- a two-way
+    // conflict on every pass-0 exchange, a quarter more shared-memory wavefronts (profiles/r02k_k1_c64_summary.json).
+    static constexpr bool ROWPAD = SFE_K1_ROWPAD && N == 4096;
+    static constexpr int PADN = ROWPAD ? N + 16 : N + N / 16;   // padded shared-memory length
     static __host__ __device__ constexpr int radix(int p) { return p < FULL ? 16 : LASTR; }
     static __host__ __device__ constexpr int size(int p)   // sub-transform length entering pass p
     {
@@ -61,12 +71,18 @@ template <int N> struct Plan {
     }
 };
 
-__device__ __forceinline__ int phi(int a) { return a + (a >> 4); }  // bank-conflict padding
+template <int N> __device__ __forceinline__ int phi(int a) { return Plan<N>::ROWPAD ? a + (a >> 8) : a + (a >> 4); }  // bank-conflict padding
 // padded index of element base + q*S: when S is a multiple of 16 the padding of the stride is a constant, so the compiler
 // keeps ONE address per thread and pass and folds q * (S + S/16) into the immediate offset of every LDS / STS
-template <int S> __device__ __forceinline__ int phi_at(int pbase, int base, int q)
+template <int N, int S> __device__ __forceinline__ int phi_at(int pbase, int base, int q)
 {
-    return S % 16 == 0 ? pbase + q * (S + S / 16) : phi(base + q * S);
+    if (Plan<N>::ROWPAD) return pbase + q * (S + S / 256);   // base + q S never leaves the row of `base` unless S = 256 (whole rows)
+    return S % 16 == 0 ? pbase + q * (S + S / 16) : phi<N>(base + q * S);
+}
+// the 16-element group thread t takes in a pass with S = 1
+template <int N> __device__ __forceinline__ int last_pass_group(int t)
+{
+    return Plan<N>::ROWPAD ? ((t & 15) << 4) | (t >> 4) : t;
 }
 
 // input flavours the kernel is compiled for (one instantiation each: no per-sample format dispatch)
@@ -173,9 +189,9 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
     constexpr int R = PL::radix(P), M = PL::size(P), S = M / R, NB = 16 / R;
 #pragma unroll
     for (int u = 0; u < NB; u++) {
-        const int beta = t + u * PL::TPF;
+        const int beta = (S == 1 ? last_pass_group<N>(t) : t) + u * PL::TPF;
         const int b = (beta / S) * M, j = P == 0 ? ((beta + c.rot_in) & (S - 1)) : beta % S;
-        const int pb = phi(b + j);
+        const int pb = phi<N>(b + j);
         float2 v[R];
         if (P == 0) {
             if (c.in_interior) {   // all loads first, conversions after: R independent requests in flight per thread
@@ -190,7 +206,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
             }
         } else {
 #pragma unroll
-            for (int k = 0; k < R; k++) v[k] = X[phi_at<S>(pb, b + j, k)];
+            for (int k = 0; k < R; k++) v[k] = X[phi_at<N, S>(pb, b + j, k)];
         }
         float2 w[16];
         if constexpr (S > 1) load_twiddles<S>(c.p.tw + PL::tw_off(P), j, w);     // (S > 1 only in radix-16 passes)
@@ -202,7 +218,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
             float2 y = v[sl];
             if (S > 1 && q != 0) y = SFE_FFT_PACKED_TWMUL ? cmul_pk(y, w[q & 15]) : cmul(y, w[q & 15]);
             if (KEEP) keep[u * R + q] = y;
-            else X[phi_at<S>(pb, b + j, q)] = y;
+            else X[phi_at<N, S>(pb, b + j, q)] = y;
         }
     }
 }
@@ -215,15 +231,15 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
     constexpr int R = PL::radix(P), M = PL::size(P), S = M / R, NB = 16 / R;
 #pragma unroll
     for (int u = 0; u < NB; u++) {
-        const int beta = t + u * PL::TPF;
+        const int beta = (S == 1 ? last_pass_group<N>(t) : t) + u * PL::TPF;
         const int b = (beta / S) * M, j = P == 0 ? ((beta + c.rot_out) & (S - 1)) : beta % S;
-        const int pb = phi(b + j);
+        const int pb = phi<N>(b + j);
         float2 v[R];
         float2 w[16];
         if constexpr (S > 1) load_twiddles<S>(c.p.tw + PL::tw_off(P), j, w);
 #pragma unroll
         for (int q = 0; q < R; q++) {
-            float2 y = FROMREG ? keep[u * R + q] : X[phi_at<S>(pb, b + j, q)];
+            float2 y = FROMREG ? keep[u * R + q] : X[phi_at<N, S>(pb, b + j, q)];
             if (S > 1 && q != 0) y = SFE_FFT_PACKED_TWMUL ? cmul_pk(y, make_float2(w[q & 15].x, -w[q & 15].y)) : cmul_conj(y, w[q & 15]);
             v[q] = y;
         }
@@ -234,7 +250,7 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
             const int k = brev<R>(sl);
             // (interpolating epilogue: the time-domain block goes back into the slots this thread has just read)
             if (P == 0 && c.p.lerp_sched == nullptr) store_output<KF>(c, b + j + k * S, v[sl]);
-            else X[phi_at<S>(pb, b + j, k)] = v[sl];
+            else X[phi_at<N, S>(pb, b + j, k)] = v[sl];
         }
     }
 }
@@ -325,7 +341,7 @@ __global__ void __launch_bounds__(Plan<N>::TPF *FPB, MINB) blkconv_fft_kernel(co
             for (int k = k_lo + t; k < k_hi; k += PL::TPF) {
                 const int2 e = __ldg(reinterpret_cast<const int2 *>(p.lerp_sched) + k);   // {pos, mu}
                 const int i = (int)((long)e.x - org);
-                const float2 a = X[phi(i)], b2 = X[phi(i + 1)];
+                const float2 a = X[phi<N>(i)], b2 = X[phi<N>(i + 1)];
                 const float w1 = __int_as_float(e.y), w0 = 1.0f - w1;
                 orow[k] = make_float2(fmaf(w1, b2.x, w0 * a.x), fmaf(w1, b2.y, w0 * a.y));
             }
