@@ -45,13 +45,15 @@ template <int N> struct Plan {
     static constexpr int LASTR = 1 << (LOGN % 4);          // 1 = none
     static constexpr int NP = FULL + (LASTR > 1 ? 1 : 0);  // passes
     static constexpr int TPF = N / 16;                     // threads per FFT
-    // Shared-memory layout.  General: one element of padding per 16 (stride-16 accesses of the last pass hit 16 banks).
-    // N = 16^3 (SFE_K1_ROWPAD): 16 rows of 256 with ONE element of padding per row, and the last pass takes its 16-element
-    // groups in transposed thread order (a half-warp then touches 16 different rows = 16 different banks).  Pass 0 lets
-    // thread t work on column (t + rot) mod 256 (Ctx::rot_in): with padding inside the rows a half-warp whose 16 columns do
-    // not start on a multiple of 16 straddles a padding slot and its first and last lane share a bank -- a two-way
-    // conflict on every pass-0 exchange, a quarter more shared-memory wavefronts (profiles/r02k_k1_c64_summary.json).
-    static constexpr bool ROWPAD = SFE_K1_ROWPAD && N == 4096;
+    // Shared-memory layout.  Small transforms: one element of padding per 16 (stride-16 accesses of the last pass hit 16
+    // banks).  N >= 1024 (SFE_K1_ROWPAD): 16 rows of N/16 elements with ONE element of padding per row, so the bank of
+    // element e is (e[3:0] + e[s0+3:s0]) mod 16 with s0 = log2 N - 4: low four bits plus low four ROW bits.  Pass 0 lets
+    // thread t work on column (t + rot) mod N/16 (Ctx::rot_in) -- with padding inside the rows a half-warp whose 16
+    // columns do not start on a multiple of 16 straddles a padding slot, its first and last lane share a bank, and every
+    // pass-0 exchange costs two wavefronts instead of one (35.8 M conflicts on 143 M ideal wavefronts,
+    // profiles/r02k_k1_c64_summary.json); with padding only between rows any 16 consecutive columns are 16 banks.
+    // The later passes keep every half-warp on 16 banks by choosing WHICH sub-transform a thread takes (BetaPerm below).
+    static constexpr bool ROWPAD = SFE_K1_ROWPAD && N >= 1024;
     static constexpr int PADN = ROWPAD ? N + 16 : N + N / 16;   // padded shared-memory length
     static __host__ __device__ constexpr int radix(int p) { return p < FULL ? 16 : LASTR; }
     static __host__ __device__ constexpr int size(int p)   // sub-transform length entering pass p
@@ -71,19 +73,66 @@ template <int N> struct Plan {
     }
 };
 
-template <int N> __device__ __forceinline__ int phi(int a) { return Plan<N>::ROWPAD ? a + (a >> 8) : a + (a >> 4); }  // bank-conflict padding
+template <int N> __device__ __forceinline__ int phi(int a)   // bank-conflict padding
+{
+    return Plan<N>::ROWPAD ? a + (a >> (Plan<N>::LOGN - 4)) : a + (a >> 4);
+}
 // padded index of element base + q*S: when S is a multiple of 16 the padding of the stride is a constant, so the compiler
 // keeps ONE address per thread and pass and folds q * (S + S/16) into the immediate offset of every LDS / STS
 template <int N, int S> __device__ __forceinline__ int phi_at(int pbase, int base, int q)
 {
-    if (Plan<N>::ROWPAD) return pbase + q * (S + S / 256);   // base + q S never leaves the row of `base` unless S = 256 (whole rows)
+    if (Plan<N>::ROWPAD) return pbase + q * (S + S / (N / 16));   // base + q S stays in the row of `base` unless S = N/16 (whole rows)
     return S % 16 == 0 ? pbase + q * (S + S / 16) : phi<N>(base + q * S);
 }
-// the 16-element group thread t takes in a pass with S = 1
-template <int N> __device__ __forceinline__ int last_pass_group(int t)
-{
-    return Plan<N>::ROWPAD ? ((t & 15) << 4) | (t >> 4) : t;
-}
+// Which sub-transform a thread takes in pass P >= 1 (row-padded layout).  Pass P works on the elements
+// e = b + j + k S (k = 0..R-1 in registers): beta = (b / M) S + j numbers the sub-transforms, and element bits
+// [sigma, sigma + rho) (sigma = log2 S, rho = log2 R) are the register index k.  The 16 lanes of a half-warp must differ
+// in (e[3:0] + e[s0+3:s0]) mod 16: lane bit i goes to element bit i where that bit is free, and to ROW bit s0 + i where
+// bit i is one of the k bits -- the two groups occupy disjoint bit positions of the sum, so the 16 lanes hit 16 banks
+// whatever k and the other bits are.  The thread's remaining index bits fill the remaining positions in order.  For
+// N = 4096 this is: passes 0 and 1 as they were, the last pass with the two nibbles of t exchanged (a transpose).
+template <int N, int P> struct BetaPerm {
+    using PL = Plan<N>;
+    static constexpr int R = PL::radix(P), S = PL::size(P) / R;
+    static constexpr int SIG = ilog2(S), RHO = ilog2(R), S0B = PL::LOGN - 4, NBITS = PL::LOGN - RHO;
+    static __host__ __device__ constexpr int dst_of_lane(int i)
+    {
+        const int T = (i >= SIG && i < SIG + RHO) ? S0B + i : i;   // element bit
+        return T < SIG ? T : T - RHO;                              // bit of beta (the k bits are not part of beta)
+    }
+    static __host__ __device__ constexpr bool lane_dst(int d)
+    {
+        return dst_of_lane(0) == d || dst_of_lane(1) == d || dst_of_lane(2) == d || dst_of_lane(3) == d;
+    }
+    static __host__ __device__ constexpr int src_of(int d)
+    {
+        for (int i = 0; i < 4; i++)
+            if (dst_of_lane(i) == d) return i;
+        int s = 4;
+        for (int x = 0; x < d; x++)
+            if (!lane_dst(x)) s++;
+        return s;
+    }
+    static __host__ __device__ constexpr int run_len(int d)
+    {
+        int len = 1;
+        while (d + len < NBITS && src_of(d + len) == src_of(d) + len) len++;
+        return len;
+    }
+    template <int D> static __device__ __forceinline__ int from(int beta)
+    {
+        if constexpr (D >= NBITS) return 0;
+        else {
+            constexpr int s = src_of(D), len = run_len(D);
+            return (((beta >> s) & ((1 << len) - 1)) << D) | from<D + len>(beta);
+        }
+    }
+    static __device__ __forceinline__ int apply(int beta)
+    {
+        if constexpr (!PL::ROWPAD || P == 0) return beta;
+        else return from<0>(beta);
+    }
+};
 
 // input flavours the kernel is compiled for (one instantiation each: no per-sample format dispatch)
 enum { KF_I16 = 0, KF_U8 = 1, KF_C64 = 2, KF_REAL = 3 };
@@ -189,7 +238,7 @@ __device__ __forceinline__ void fwd_pass(float2 *X, int t, const Ctx &c, float2 
     constexpr int R = PL::radix(P), M = PL::size(P), S = M / R, NB = 16 / R;
 #pragma unroll
     for (int u = 0; u < NB; u++) {
-        const int beta = (S == 1 ? last_pass_group<N>(t) : t) + u * PL::TPF;
+        const int beta = BetaPerm<N, P>::apply(t + u * PL::TPF);
         const int b = (beta / S) * M, j = P == 0 ? ((beta + c.rot_in) & (S - 1)) : beta % S;
         const int pb = phi<N>(b + j);
         float2 v[R];
@@ -231,7 +280,7 @@ __device__ __forceinline__ void inv_pass(float2 *X, int t, const Ctx &c, float2 
     constexpr int R = PL::radix(P), M = PL::size(P), S = M / R, NB = 16 / R;
 #pragma unroll
     for (int u = 0; u < NB; u++) {
-        const int beta = (S == 1 ? last_pass_group<N>(t) : t) + u * PL::TPF;
+        const int beta = BetaPerm<N, P>::apply(t + u * PL::TPF);
         const int b = (beta / S) * M, j = P == 0 ? ((beta + c.rot_out) & (S - 1)) : beta % S;
         const int pb = phi<N>(b + j);
         float2 v[R];
