@@ -16,7 +16,7 @@ LIB = os.path.join(PKG, "libsfegpu.so")
 
 CU_SOURCES = ["capi.cu", "chain.cu", "blkconv_kernel.cu", "polyphase_kernel.cu", "util_kernels.cu", "toeplitz_mma_kernel.cu", "fused_bank_kernel.cu", "ring.cu", "bpsk_tx_kernel.cu", "bpsk_tx.cu", "feed.cu", "box.cu", "no_alloc.cu"]
 CPP_SOURCES = ["schedule.cpp"]
-HEADERS = ["kernels.h", "schedule.h", "sfe_common.cuh", "sfe_fft.cuh", "../../include/sfe_gpu.h"]
+HEADERS = ["kernels.h", "schedule.h", "sfe_common.cuh", "sfe_fft.cuh", "sfe_fft_plan.h", "../../include/sfe_gpu.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

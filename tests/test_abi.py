@@ -118,3 +118,17 @@ def test_schedule_closed_form_runs_match_the_sequential_walk():
         for seed in (1, 2, 3):
             r = subprocess.run([exe, str(seed), "1500"], capture_output=True, text=True)
             assert r.returncode == 0 and r.stdout.startswith("ok:"), r.stdout
+
+
+def test_fft_shared_memory_layout_is_conflict_free():
+    """K1's row-padded shared-memory layout and its per-pass assignment of sub-transforms to threads
+    (csrc/sfe_fft_plan.h): every half-warp access of every pass hits 16 banks, for every column rotation of pass 0;
+    checked on the host by tests/cpp/fft_layout_check.cxx from the very header the kernel is compiled with"""
+    import subprocess
+    import tempfile
+    csrc = os.path.join(ROOT, "simplefe_b200", "csrc")
+    with tempfile.TemporaryDirectory() as td:
+        exe = os.path.join(td, "fft_layout_check")
+        subprocess.run(["g++", "-O1", "-std=c++17", "-I", csrc, os.path.join(ROOT, "tests", "cpp", "fft_layout_check.cxx"), "-o", exe], check=True)
+        r = subprocess.run([exe], capture_output=True, text=True)
+        assert r.returncode == 0 and "OK:" in r.stdout, r.stdout
