@@ -106,7 +106,8 @@ struct sfe_chain {
     int dev = 0, S = 0, in_fmt = 0, flags = 0;
     std::vector<Op> ops;
     int cur = 0;                   // which history buffer holds the live state
-    Workspace ws[2];
+    Workspace ws[4];               // [0] also serves process_dev; process_host rotates over the first n_ws
+    int n_ws = 3;
     std::string plan;
     bool profile = false;          // bracket the main kernels of THIS call with events
     int profile_every = 0;         // 0 = off, n = every n-th process call
@@ -829,7 +830,9 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
         fmt = SFE_IN_F32;
     }
     for (Op &op : c->ops) ok = ok && alloc_hist(op, c->S) && (op.kind != OP_BANK || make_bank_tables(op));
-    for (int i = 0; i < 2 && ok; i++) ok = SFE_CUDA(cudaStreamCreateWithFlags(&c->ws[i].st, cudaStreamNonBlocking));
+    static const int n_ws_env = getenv("SFE_HOST_WORKSPACES") ? atoi(getenv("SFE_HOST_WORKSPACES")) : 0;   // tuning hook
+    c->n_ws = n_ws_env >= 2 && n_ws_env <= 4 ? n_ws_env : 3;
+    for (int i = 0; i < 4 && ok; i++) ok = SFE_CUDA(cudaStreamCreateWithFlags(&c->ws[i].st, cudaStreamNonBlocking));
     // every table, history fill and spectrum above is on the device before the first process call may read it
     ok = ok && SFE_CUDA(cudaDeviceSynchronize());
     if (!ok) {
@@ -1020,7 +1023,9 @@ extern "C" int sfe_chain_process_host(sfe_chain *c, const void *h_in, long n_in,
 static int process_host_groups(sfe_chain *c, const void *h_in, long n_in, long in_pitch, void *h_out, long out_pitch, long no)
 {
     const int eb = fmt_bytes(c->in_fmt);
-    // stream groups of ~64 MiB input: H2D(g+1) overlaps kernels(g) overlaps D2H(g-1) on two CUDA streams
+    // stream groups of ~64 MiB input: H2D(g+1) overlaps kernels(g) overlaps D2H(g-1) on n_ws CUDA streams with a staging
+    // buffer each.  Two leave each copy engine idle while the other stream's group is in its kernels or its own opposite
+    // copy; with three the H2D engine always has a group queued (measured on cfg 1, whose output is as large as its input).
     const size_t row_in = (size_t)n_in * eb;
     const long dpitch = (n_in + 7) & ~7L;   // device staging rows start 16-byte aligned in every format (TMA)
     static const long group_mb = getenv("SFE_HOST_GROUP_MB") ? atol(getenv("SFE_HOST_GROUP_MB")) : 64;   // tuning hook
@@ -1028,13 +1033,14 @@ static int process_host_groups(sfe_chain *c, const void *h_in, long n_in, long i
     if (gs < 1) gs = 1;
     if (gs > c->S) gs = c->S;
     if (c->S >= 4 && gs > (c->S + 3) / 4) gs = (c->S + 3) / 4;  // at least 4 groups so that copies overlap
+    if (c->S >= 2 * c->n_ws && gs > (c->S + 2 * c->n_ws - 1) / (2 * c->n_ws)) gs = (c->S + 2 * c->n_ws - 1) / (2 * c->n_ws);
     int rc = upload_schedules(c, c->ws[0].st);
     if (rc != SFE_OK) return rc;
     if (!SFE_CUDA(cudaStreamSynchronize(c->ws[0].st))) return SFE_ERR_CUDA;
     const long opitch = no > 0 ? no : 1;
     int g = 0;
     for (int s0 = 0; s0 < c->S; s0 += gs, g++) {
-        Workspace &w = c->ws[g & 1];
+        Workspace &w = c->ws[g % c->n_ws];
         const int ns = c->S - s0 < gs ? c->S - s0 : gs;
         if (!ensure(&w.d_in, &w.in_bytes, (size_t)gs * dpitch * eb) ||
             !ensure(&w.d_out, &w.out_bytes, sizeof(float2) * (size_t)gs * opitch))
