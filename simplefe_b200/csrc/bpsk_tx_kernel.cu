@@ -29,6 +29,20 @@ constexpr int TX_WSYM = 32 * TX_GROUP;   // symbols per warp
 constexpr int TX_MAXM = 32;        // taps per phase, at most (n_taps <= 32 * sps)
 constexpr int TX_MAXW = 4;         // warps per CTA, at most
 
+typedef unsigned long long tx_f32x2;
+__device__ __forceinline__ tx_f32x2 tx_pack2(float lo, float hi)
+{
+    tx_f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ tx_f32x2 tx_ffma2(tx_f32x2 a, tx_f32x2 b, tx_f32x2 c)
+{
+    tx_f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
 // bit k of the channel's symbol stream; k < 0 reads the history word (bit 63 = symbol -1)
 __device__ __forceinline__ uint64_t bits_window(const uint32_t *cur, uint64_t hist, long s_hi, long n_sym)
 {
@@ -67,9 +81,13 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
     const uint64_t hw = hist[ch];
     const int M = (n_taps + sps - 1) / sps;                // taps per phase
 
+    // Even sps: the taps of phases 2r' and 2r'+1 sit side by side, hs[((r' MT) + m) 2 + (r & 1)], so that one 64-bit
+    // register pair (h[2r'][m], h[2r'+1][m]) times a broadcast sign is ONE FFMA2 for two output samples of a symbol.
+    const bool paired = (sps & 1) == 0;
+    auto tap_at = [&](int r, int m) { return paired ? (((r >> 1) * MT + m) << 1) + (r & 1) : r * MT + m; };
     for (int i = threadIdx.x; i < sps * MT; i += blockDim.x) {
         const int r = i / MT, m = i - r * MT;
-        hs[i] = (m < M && r + m * sps < n_taps) ? amp * __ldg(taps + r + m * sps) : 0.f;
+        hs[tap_at(r, m)] = (m < M && r + m * sps < n_taps) ? amp * __ldg(taps + r + m * sps) : 0.f;
     }
     __syncthreads();
     if (s0 >= n_sym) return;                               // whole warp
@@ -92,6 +110,34 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
                 const uint32_t word = bit < 32 ? wl : wh;
                 sg[d] = __uint_as_float(0x3F800000u | ((word << (31 - (bit & 31))) & 0x80000000u));
             }
+            if (paired) {
+                // two phases per round: same FP32-pipe time as scalar FFMAs, half the issue slots (the kernel was issue
+                // bound: 85 % of the slots, 62 % of them FFMA).  Each lane of an FFMA2 is the IEEE fma of the scalar loop
+                // below, taps in the same order: the samples are bit-identical.
+                for (int r = 0; r < sps; r += 2) {
+                    tx_f32x2 acc[TX_GROUP];
+#pragma unroll
+                    for (int i = 0; i < TX_GROUP; i++) acc[i] = 0ull;
+                    const ulonglong2 *hr = reinterpret_cast<const ulonglong2 *>(hs + r * MT);   // pairs m, m + 1 per 128-bit load
+#pragma unroll
+                    for (int m2 = 0; m2 < MT / 2; m2++) {
+                        const ulonglong2 h2 = hr[m2];
+#pragma unroll
+                        for (int u = 0; u < 2; u++) {
+                            const int m = 2 * m2 + u;
+                            const tx_f32x2 hp = u == 0 ? h2.x : h2.y;
+#pragma unroll
+                            for (int i = 0; i < TX_GROUP; i++) {
+                                const float sgn = sg[i - m + MT - 1];
+                                acc[i] = tx_ffma2(hp, tx_pack2(sgn, sgn), acc[i]);
+                            }
+                        }
+                    }
+                    tx_f32x2 *tr = reinterpret_cast<tx_f32x2 *>(trow + r);                      // sps and gstride are even: 8-byte aligned
+#pragma unroll
+                    for (int i = 0; i < TX_GROUP; i++) tr[i * (sps >> 1)] = acc[i];
+                }
+            } else
             for (int r = 0; r < sps; r++) {
                 float acc[TX_GROUP];
 #pragma unroll
@@ -120,7 +166,7 @@ bpsk_tx_kernel(const uint32_t *bits, long pitch_words, const uint64_t *hist, int
 #pragma unroll
                 for (int i = 0; i < TX_GROUP; i++) acc[i] = 0.f;
                 for (int m = 0; m < M; m++) {
-                    const uint32_t hb = __float_as_uint(hs[r * MT + m]);
+                    const uint32_t hb = __float_as_uint(hs[tap_at(r, m)]);
 #pragma unroll
                     for (int i = 0; i < TX_GROUP; i++) {
                         const long sm = s_first + i - m;                       // symbol s - m
