@@ -106,8 +106,13 @@ template <int KF> __device__ __forceinline__ void store_output(const Ctx &c, int
 // the other eleven are products of those, at most three multiplications deep (relative error < 3e-7, two orders inside
 // the parity budget).  With fifteen loads per thread and pass the twiddle rows were 18 % of this kernel's LSU
 // wavefronts, and the LSU data pipe is what bounds it (profiles/r02_ncu_k1_c64_before.json: 79.5 % of peak).
+// data x twiddle as FMUL2 + FFMA2 instead of four scalar instructions: slower while the shared-memory bank conflicts kept the
+// LSU pipe as the bound (1.36 vs 1.23 ms), faster since the row layout removed them (cfg 1 int16 2.267 -> 2.163 ms)
 #ifndef SFE_FFT_PACKED_TWMUL
-#define SFE_FFT_PACKED_TWMUL 0     // data x twiddle as FMUL2 + FFMA2 instead of four scalar instructions (tuning switch)
+#define SFE_FFT_PACKED_TWMUL 1
+#endif
+#ifndef SFE_FFT_PACKED_HMUL
+#define SFE_FFT_PACKED_HMUL 0      // the same for the tap-spectrum multiply (tuning switch)
 #endif
 #ifndef SFE_FFT_TW_PRODUCTS
 #define SFE_FFT_TW_PRODUCTS 1
@@ -288,7 +293,8 @@ __global__ void __launch_bounds__(Plan<N>::TPF *FPB, MINB) blkconv_fft_kernel(co
     for (int u = 0; u < NB; u++)
 #pragma unroll
         for (int q = 0; q < RL; q++)
-            keep[u * RL + q] = cmul(keep[u * RL + q], __ldg(p.hp + (u * RL + q) * PL::TPF + t));
+            keep[u * RL + q] = SFE_FFT_PACKED_HMUL ? cmul_pk(keep[u * RL + q], __ldg(p.hp + (u * RL + q) * PL::TPF + t))
+                                                   : cmul(keep[u * RL + q], __ldg(p.hp + (u * RL + q) * PL::TPF + t));
 
     InvChain<N, PL::NP - 1, KF>::run(X, t, c, keep);
 
