@@ -189,18 +189,27 @@ __device__ __forceinline__ void bf_scaled(cpx2 &a, cpx2 &b)            // (a, b)
     a = s;
     b = d;
 }
+// the four sixteenth-turn twiddles of stage 1: scalar (2 FMUL + 2 FFMA) or packed (FMUL2 + FFMA2, tuning switch)
+#ifndef SFE_FFT_PACKED_W16
+#define SFE_FFT_PACKED_W16 0
+#endif
+template <int M16, int SIGN> __device__ __forceinline__ cpx2 mul_w16_pk(cpx2 d)
+{
+    if (SFE_FFT_PACKED_W16) return cmul2_pk(d, make_float2(kCos16[M16], SIGN > 0 ? kSin16[M16] : -kSin16[M16]));
+    return cpack(mul_w16<M16, SIGN>(cunpack(d)));
+}
 template <int SIGN> __device__ __forceinline__ void dft16_dif_packed_deferred(cpx2 (&v)[16])
 {
     // stage 1: pairs (I, I + 8), twiddle w16^I; slots 10 and 14 leave with h pending
 #pragma unroll
     for (int I = 0; I < 8; I++) bf_plain(v[I], v[I + 8]);
-    v[9] = cpack(mul_w16<1, SIGN>(cunpack(v[9])));
+    v[9] = mul_w16_pk<1, SIGN>(v[9]);
     v[10] = mul_p1<SIGN>(v[10]);
-    v[11] = cpack(mul_w16<3, SIGN>(cunpack(v[11])));
+    v[11] = mul_w16_pk<3, SIGN>(v[11]);
     v[12] = mul_i<SIGN>(v[12]);
-    v[13] = cpack(mul_w16<5, SIGN>(cunpack(v[13])));
+    v[13] = mul_w16_pk<5, SIGN>(v[13]);
     v[14] = mul_m1<SIGN>(v[14]);
-    v[15] = cpack(mul_w16<7, SIGN>(cunpack(v[15])));
+    v[15] = mul_w16_pk<7, SIGN>(v[15]);
     // stage 2: pairs (G + I, G + I + 4), twiddle w16^(2 I); (10, 14) both carry h; 5, 7, 13, 15 leave with h pending
 #pragma unroll
     for (int G = 0; G < 16; G += 8) {
