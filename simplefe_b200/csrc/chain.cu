@@ -107,7 +107,7 @@ struct sfe_chain {
     std::vector<Op> ops;
     int cur = 0;                   // which history buffer holds the live state
     Workspace ws[4];               // [0] also serves process_dev; process_host rotates over the first n_ws
-    int n_ws = 3;
+    int n_ws = 2;
     std::string plan;
     bool profile = false;          // bracket the main kernels of THIS call with events
     int profile_every = 0;         // 0 = off, n = every n-th process call
@@ -831,7 +831,7 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
     }
     for (Op &op : c->ops) ok = ok && alloc_hist(op, c->S) && (op.kind != OP_BANK || make_bank_tables(op));
     static const int n_ws_env = getenv("SFE_HOST_WORKSPACES") ? atoi(getenv("SFE_HOST_WORKSPACES")) : 0;   // tuning hook
-    c->n_ws = n_ws_env >= 2 && n_ws_env <= 4 ? n_ws_env : 3;
+    c->n_ws = n_ws_env >= 2 && n_ws_env <= 4 ? n_ws_env : 2;
     for (int i = 0; i < 4 && ok; i++) ok = SFE_CUDA(cudaStreamCreateWithFlags(&c->ws[i].st, cudaStreamNonBlocking));
     // every table, history fill and spectrum above is on the device before the first process call may read it
     ok = ok && SFE_CUDA(cudaDeviceSynchronize());
@@ -1024,8 +1024,7 @@ static int process_host_groups(sfe_chain *c, const void *h_in, long n_in, long i
 {
     const int eb = fmt_bytes(c->in_fmt);
     // stream groups of ~64 MiB input: H2D(g+1) overlaps kernels(g) overlaps D2H(g-1) on n_ws CUDA streams with a staging
-    // buffer each.  Two leave each copy engine idle while the other stream's group is in its kernels or its own opposite
-    // copy; with three the H2D engine always has a group queued (measured on cfg 1, whose output is as large as its input).
+    // buffer each (two; three and four were measured within the run-to-run spread of the box: profiles/r02_host_workspaces.json)
     const size_t row_in = (size_t)n_in * eb;
     const long dpitch = (n_in + 7) & ~7L;   // device staging rows start 16-byte aligned in every format (TMA)
     static const long group_mb = getenv("SFE_HOST_GROUP_MB") ? atol(getenv("SFE_HOST_GROUP_MB")) : 64;   // tuning hook
