@@ -713,7 +713,7 @@ def main():
         dt = max_ranks(time.perf_counter() - t0)
         e2e = {"value": S_total * N * k_e2e / dt / 1e6, "unit": METRIC,
                "h2d_bytes_per_step": int(S * N * eb), "d2h_bytes_per_step": int(S * n_h * 8), "steps": k_e2e,
-               "api": "sfe_chain_process_host (pinned host in/out, 2 CUDA streams, stream groups double-buffered)"}
+               "api": "sfe_chain_process_host (pinned host in/out, stream groups double-buffered over 2 CUDA streams)"}
         # what the box can do at best: one plain pinned H2D copy of the same bytes per GPU, all GPUs at once
         barrier()
         t0 = time.perf_counter()
