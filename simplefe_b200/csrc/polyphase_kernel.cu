@@ -463,6 +463,21 @@ template <> __device__ __forceinline__ float2 ls_cvt<SFE_IN_F32>(f32x2 w)
     return r;
 }
 
+// staging of complex64 rows: round IT copies samples 32 IT + lane of the warp's eight rows, every offset an immediate
+constexpr int LS_ROUNDS = 8;                                                // 256 samples: the largest span a 64 KB tile holds
+template <int IT, int RR, class RT>
+__device__ __forceinline__ void ls_cp_rounds(uint32_t dst0, const RT *const (&src)[32 / LS_WARPS], int span, int lane)
+{
+    if constexpr (IT < LS_ROUNDS) {
+        if (RR == 0 && IT * 32 >= span) return;                             // warp uniform: no later round has work
+        if (IT * 32 + lane < span)
+            asm volatile("cp.async.ca.shared.global [%0 + %2], [%1 + %3], 8;" ::"r"(dst0), "l"(src[RR]),
+                         "n"(IT * 32 * LS_PITCH * 8 + LS_WARPS * RR * 8), "n"(IT * 32 * (int)sizeof(RT)) : "memory");
+        if constexpr (RR + 1 < 32 / LS_WARPS) ls_cp_rounds<IT, RR + 1>(dst0, src, span, lane);
+        else ls_cp_rounds<IT + 1, 0>(dst0, src, span, lane);
+    }
+}
+
 template <int FMT, bool GRP>
 __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
 {
@@ -525,11 +540,20 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
         if (FMT == SFE_IN_F32) {
             // complex64 rows need no conversion: 8-byte asynchronous copies straight into the transposed tile, the whole
             // span of the CTA in flight at once instead of 16 loads per lane and round
-            for (int i0 = lane; i0 < span; i0 += 32) {
+            // (rounds unrolled with every offset an immediate of one shared-memory address and eight row pointers: the
+            // per-copy address arithmetic was 16 % of the kernel's instructions)
+            const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(xs + lane * LS_PITCH + warp);
 #pragma unroll
-                for (int rr = 0; rr < 32 / LS_WARPS; rr++) {
-                    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(xs + i0 * LS_PITCH + warp + LS_WARPS * rr);
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src[rr] + i0) : "memory");
+            for (int rr = 0; rr < 32 / LS_WARPS; rr++) src[rr] += lane;
+            if (span <= 32 * LS_ROUNDS) {
+                ls_cp_rounds<0, 0>(dst0, src, span, lane);
+            } else {
+                for (int i0 = lane; i0 < span; i0 += 32) {
+#pragma unroll
+                    for (int rr = 0; rr < 32 / LS_WARPS; rr++) {
+                        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(xs + i0 * LS_PITCH + warp + LS_WARPS * rr);
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src[rr] + i0 - lane) : "memory");
+                    }
                 }
             }
             asm volatile("cp.async.commit_group;\n cp.async.wait_group 0;" ::: "memory");
@@ -665,11 +689,27 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
     }
     __syncthreads();
     const int nk = (int)(k1 - k0 + 1);
-    for (int r = warp; r < 32; r += LS_WARPS) {
-        const int s = s0 + r;
-        if (s >= p.n_streams) continue;
-        f32x2 *o = reinterpret_cast<f32x2 *>(p.out) + (long)s * p.out_pitch + k0;
-        for (int kl = lane; kl < nk; kl += 32) o[kl] = ob[r * opitch + kl];
+    f32x2 *o0 = reinterpret_cast<f32x2 *>(p.out) + (long)(s0 + warp) * p.out_pitch + k0;
+    if (nk <= 64 && (nk & 1) == 0 && (p.out_pitch & 1) == 0 && (reinterpret_cast<uintptr_t>(o0) & 15) == 0) {
+        // whole tiles (the common case): a lane takes two consecutive outputs of a row, all 8 rows of the warp unrolled --
+        // one 128-bit store per row and lane instead of two 64-bit ones under a loop with its own index arithmetic
+        // (that loop was 14 % of the kernel's instructions, more than the filter itself: profiles/r02m_cfg4_k2s_summary.json)
+        const bool mine = 2 * lane < nk;
+        const f32x2 *ol = ob + warp * opitch + 2 * lane;
+#pragma unroll
+        for (int rr = 0; rr < 32 / LS_WARPS; rr++) {
+            if (mine && s0 + warp + LS_WARPS * rr < p.n_streams) {
+                const f32x2 a = ol[rr * LS_WARPS * opitch], b = ol[rr * LS_WARPS * opitch + 1];
+                *reinterpret_cast<ulonglong2 *>(o0 + (long)rr * LS_WARPS * p.out_pitch + 2 * lane) = make_ulonglong2(a, b);
+            }
+        }
+    } else {
+        for (int r = warp; r < 32; r += LS_WARPS) {
+            const int s = s0 + r;
+            if (s >= p.n_streams) continue;
+            f32x2 *o = reinterpret_cast<f32x2 *>(p.out) + (long)s * p.out_pitch + k0;
+            for (int kl = lane; kl < nk; kl += 32) o[kl] = ob[r * opitch + kl];
+        }
     }
 }
 
