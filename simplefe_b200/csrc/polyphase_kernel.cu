@@ -585,8 +585,18 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
         // by half or more): their combined taps are laid out on one sample axis, m = newest sample of the run - sample,
         // as rows of LS_G (c, c) pairs, zero outside each output's window.  Per sample one LDS.64 of the lane's own
         // stream and two broadcast LDS.128 feed LS_G FFMA2 -- 4 shared-memory wavefronts instead of 10.
-        ulonglong2 *ct = reinterpret_cast<ulonglong2 *>(ls_sm + p.tap_bytes + warp * p.cw_bytes);   // [rows][LS_G / 2]
+        float4 *ct = reinterpret_cast<float4 *>(ls_sm + p.tap_bytes + warp * p.cw_bytes);   // [rows] of LS_G combined taps
         const int g = lane & (LS_G - 1);
+        // the window of every output of the warp, derived once by the lane that holds its schedule entry (one division per
+        // lane instead of one per lane and run): row of x[n_top] in the staged span, and ph0 | d << 16
+        int row_l = 0, phd_l = 0;
+        {
+            const int n0 = (int)floordiv(pos_li, p.up);
+            const int ph0 = pos_li - n0 * p.up;
+            const int d = ph0 + 1 == p.up ? 1 : 0;
+            row_l = (int)(n0 + d - n_lo);
+            phd_l = ph0 | (d << 16);
+        }
 #pragma unroll
         for (int qq = 0; qq < LS_KPW / LS_G; qq++) {
 #pragma unroll
@@ -594,14 +604,12 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
             const long kg = k0 + kl_of(qq * LS_G);
             if (kg > k1) continue;                                         // warp uniform
             // every lane derives the window of output g = lane % LS_G of the run
-            const int pos = __shfl_sync(0xffffffffu, pos_li, qq * LS_G + g);
+            const int row = __shfl_sync(0xffffffffu, row_l, qq * LS_G + g);
+            const int phd = __shfl_sync(0xffffffffu, phd_l, qq * LS_G + g);
             const float mu = __shfl_sync(0xffffffffu, mu_l, qq * LS_G + g);
             const bool valid = kg + g <= k1;
-            const int n0 = (int)floordiv(pos, p.up);
-            const int ph0 = pos - n0 * p.up;
-            int ph1 = ph0 + 1, d = 0;
-            if (ph1 == p.up) { ph1 = 0; d = 1; }
-            const int row = (int)(n0 + d - n_lo);                          // row of x[n_top] in the staged span
+            const int ph0 = phd & 0xffff, d = phd >> 16;
+            const int ph1 = d ? 0 : ph0 + 1;
             const int row_hi = __reduce_max_sync(0xffffffffu, valid ? row : 0);
             const int off = row_hi - row;
             int M = __reduce_max_sync(0xffffffffu, valid ? off + J + d : 0);
@@ -612,29 +620,30 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
             const float *t0 = tp + ph0 * J, *t1 = tp + ph1 * J;
             const float w0 = 1.0f - mu;
             __syncwarp();                                                  // the previous run's readers are done
-            f32x2 *cf = reinterpret_cast<f32x2 *>(ct);
+            float *cf = reinterpret_cast<float *>(ct);
             for (int m = lane / LS_G; m < M; m += 32 / LS_G) {
                 const int i = m - off;
                 const float a = (valid && i >= 0 && i < J) ? t1[i] : 0.f;
                 const float b = (valid && i - d >= 0 && i - d < J) ? t0[i - d] : 0.f;
-                const float c = mu != 0.f ? fmaf(mu, a, w0 * b) : b;
-                cf[m * LS_G + g] = d_pack2(c, c);
+                cf[m * LS_G + g] = mu != 0.f ? fmaf(mu, a, w0 * b) : b;
             }
             __syncwarp();
             const f32x2 *xq = reinterpret_cast<const f32x2 *>(xs + row_hi * LS_PITCH + lane);
-            const ulonglong2 *cq = ct;
+            const float4 *cq = ct;
             f32x2 a0 = 0ull, a1 = 0ull, a2 = 0ull, a3 = 0ull;
-            for (int m = 0; m < M; m += 2, xq -= 2 * LS_PITCH, cq += LS_G) {
+            // the taps are scalars: ptxas folds the (c, c) broadcast into the .F32 operand selector of FFMA2, so one
+            // broadcast LDS.128 carries the four taps of a sample row (they were (c, c) pairs: two loads per row)
+            for (int m = 0; m < M; m += 2, xq -= 2 * LS_PITCH, cq += 2) {
                 const f32x2 x0 = xq[0], x1 = xq[-LS_PITCH];
-                const ulonglong2 c01 = cq[0], c23 = cq[1], e01 = cq[2], e23 = cq[3];
-                a0 = d_ffma2(c01.x, x0, a0);
-                a1 = d_ffma2(c01.y, x0, a1);
-                a2 = d_ffma2(c23.x, x0, a2);
-                a3 = d_ffma2(c23.y, x0, a3);
-                a0 = d_ffma2(e01.x, x1, a0);
-                a1 = d_ffma2(e01.y, x1, a1);
-                a2 = d_ffma2(e23.x, x1, a2);
-                a3 = d_ffma2(e23.y, x1, a3);
+                const float4 c = cq[0], e = cq[1];
+                a0 = d_ffma2(d_pack2(c.x, c.x), x0, a0);
+                a1 = d_ffma2(d_pack2(c.y, c.y), x0, a1);
+                a2 = d_ffma2(d_pack2(c.z, c.z), x0, a2);
+                a3 = d_ffma2(d_pack2(c.w, c.w), x0, a3);
+                a0 = d_ffma2(d_pack2(e.x, e.x), x1, a0);
+                a1 = d_ffma2(d_pack2(e.y, e.y), x1, a1);
+                a2 = d_ffma2(d_pack2(e.z, e.z), x1, a2);
+                a3 = d_ffma2(d_pack2(e.w, e.w), x1, a3);
             }
             res[qq * LS_G + 0] = a0;
             res[qq * LS_G + 1] = a1;
