@@ -691,13 +691,19 @@ __global__ void __launch_bounds__(LS_NT) poly_lanes_kernel(const PolyParams p)
     __syncthreads();                                                       // all reads of xs are done: reuse it
     f32x2 *ob = reinterpret_cast<f32x2 *>(xs);                             // [32 streams][kt + 1]
     const int opitch = p.kt + 1;
+    const int nk = (int)(k1 - k0 + 1);
+    {
+        // slot q of warp w is output kl_of(q) = w_first + (a constant of q): one pointer, immediate offsets, 32-bit bounds
+        const int w_first = GRP ? LS_G * warp : warp;
+        f32x2 *obl = ob + lane * opitch + w_first;
+        const int left = nk - w_first;
 #pragma unroll
-    for (int q = 0; q < LS_KPW; q++) {
-        const int kl = kl_of(q);
-        if (k0 + kl <= k1) ob[lane * opitch + kl] = res[q];
+        for (int q = 0; q < LS_KPW; q++) {
+            const int rel = GRP ? LS_G * LS_WARPS * (q / LS_G) + (q % LS_G) : LS_WARPS * q;
+            if (rel < left) obl[rel] = res[q];
+        }
     }
     __syncthreads();
-    const int nk = (int)(k1 - k0 + 1);
     f32x2 *o0 = reinterpret_cast<f32x2 *>(p.out) + (long)(s0 + warp) * p.out_pitch + k0;
     if (nk <= 64 && (nk & 1) == 0 && (p.out_pitch & 1) == 0 && (reinterpret_cast<uintptr_t>(o0) & 15) == 0) {
         // whole tiles (the common case): a lane takes two consecutive outputs of a row, all 8 rows of the warp unrolled --
