@@ -43,7 +43,7 @@ def test_select_bits_follows_the_reference_block_structure():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("tapname,sps,fft", [("rrc111", 10, 2048), ("rrc551", 50, 8192)])
+@pytest.mark.parametrize("tapname,sps,fft", [("rrc111", 10, 2048), ("rrc551", 50, 8192), ("rrc111", 7, 2048)])   # even sps: packed two-phase loop; odd: scalar
 def test_bpsk_tx_vs_reference_chain(gpu_lib, oracle_lib, tapname, sps, fft):
     from oracle import oracle as O
     from simplefe_b200.bpsk import SCALING_FACTOR, TX_DAC10, TX_F32, BpskTx, select_bits
