@@ -156,9 +156,9 @@ bool make_decim(Op &op, const std::vector<double> &g, int D)
     return upload(&op.d_gp, gp);
 }
 
-bool make_toep(Op &op, const std::vector<double> &g)
+bool make_toep(Op &op, const std::vector<double> &g, int in_fmt)
 {
-    if (!toeplitz_prepare(g, op.toep)) return false;
+    if (!toeplitz_prepare(g, op.toep, in_fmt)) return false;
     op.kind = OP_TOEP;
     op.D = 8;
     op.T = (int)g.size();
@@ -802,11 +802,12 @@ static sfe_chain * sfe_chain_create_impl(const sfe_chain_desc *d)
             }
             // tensor cores: many streams sharing the filter, or a FEW long streams (each row is time-split over the tile rows;
             // short calls of fewer than 8 streams fall back to the CUDA-core FIR at run time, so that op carries both tap images)
-            const bool tensor = !(d->flags & SFE_FLAG_NO_TENSOR) && fmt == SFE_IN_I16 && step / s.up == 8 &&
-                                (int)g.size() <= toeplitz_max_taps();
+            // (u8 rows -- one signed byte per component -- run on the same kernel from 8 streams on; fewer keep the CUDA-core FIR)
+            const bool tensor = !(d->flags & SFE_FLAG_NO_TENSOR) && (fmt == SFE_IN_I16 || (fmt == SFE_IN_U8 && d->n_streams >= 8)) &&
+                                step / s.up == 8 && (int)g.size() <= toeplitz_max_taps();
             const bool both = tensor && d->n_streams < 8;
             if (both) ok = ok && make_decim(op, g, (int)(step / s.up));
-            if (tensor && make_toep(op, g)) {
+            if (tensor && make_toep(op, g, fmt)) {
                 c->plan += both ? "[toeplitz_i8_tcgen05 time-split | decim_fir for short calls]" : "[toeplitz_i8_tcgen05]";
             } else if (!both) {
                 ok = ok && make_decim(op, g, (int)(step / s.up));

@@ -78,7 +78,7 @@ struct ToepParams {
     long n_first;         // y[k] = sum_j g[j] x[n_first + 8k - j]
     int KB;               // 128-byte K-blocks per window = ceil((T-1)/128) + 1
     const int8_t *bmat;   // device image of the B operand tiles (toeplitz_prepare)
-    float w[3];           // digit weights (include max|g| / Zmax / 32767)
+    float w[3];           // digit weights (include max|g| / Zmax and the input scale 1/32767 or 1/127)
     float corr[3];        // 128 * sum_j d_tau[j]
     // filled by launch_toeplitz
     int ring, n_groups;
@@ -90,7 +90,7 @@ struct ToepHost {
     float w[3] = {0, 0, 0}, corr[3] = {0, 0, 0};
     std::vector<int8_t> bmat;
 };
-bool toeplitz_prepare(const std::vector<double> &g, ToepHost &h);
+bool toeplitz_prepare(const std::vector<double> &g, ToepHost &h, int in_fmt = SFE_IN_I16);
 int toeplitz_max_taps();
 int launch_toeplitz(const ToepParams &p, cudaStream_t st);
 

@@ -16,6 +16,11 @@
 // arithmetic is exact; the only approximation is the 2^-23 (relative to the largest tap) tap quantisation.
 // The epilogue recombines  y = sum_tau w_tau * (256*(A_hi - 128*sum d_tau) + A_lo)  in fp32.
 //
+// u8 rows (the device's wire format, offset-binary I,Q bytes): sample b is the int16 value b - 128, i.e. lo plane
+// b ^ 0x80 and hi plane its sign extension; the producers build those two planes straight from the bytes (4 PRMT + 4 LOP
+// per 4 samples), the staged K-block is half as large, and everything behind the operand tiles is the int16 kernel with
+// the scale 1/127 in place of 1/32767 (toeplitz_prepare).
+//
 // Persistent, warp-specialised CTA (two per SM):
 //   warps 0-3  epilogue   tcgen05.ld of the int32 accumulators, digit/byte recombination, float2 stores
 //   warp  4    MMA issue  one thread; tcgen05.mma.cta_group::1.kind::i8, commits to mbarriers
@@ -144,8 +149,35 @@ __device__ __forceinline__ uint32_t load_i16(const ToepParams &p, int s, long n)
     return h < 0 ? 0u : __ldg(reinterpret_cast<const uint32_t *>(p.in.hist) + (long)s * p.in.H + h);
 }
 
+// prmt.b32 in its default mode (__byte_perm only defines the low three bits of a selector nibble)
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+
+// u8 sample as the int16 pair word the int16 path loads: (b - 128) sign extended, I in the low half
+__device__ __forceinline__ uint32_t load_u8_as_i16(const ToepParams &p, int s, long n)
+{
+    if (s >= p.n_streams || n >= p.in.n) return 0u;
+    uint32_t w;
+    if (n >= 0) w = __ldg(reinterpret_cast<const uint16_t *>(p.in.cur) + (long)s * p.in.pitch + n);
+    else {
+        const long h = (long)p.in.H + n;
+        if (h < 0) return 0u;
+        w = __ldg(reinterpret_cast<const uint16_t *>(p.in.hist) + (long)s * p.in.H + h);
+    }
+    const int i = (int)(w & 0xFF) - 128, q = (int)(w >> 8) - 128;
+    return ((uint32_t)i & 0xFFFFu) | ((uint32_t)q << 16);
+}
+
+template <int FMT>
 __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_constant__ CUtensorMap map_cur, const ToepParams p)
 {
+    constexpr bool U8 = FMT == SFE_IN_U8;
+    constexpr int ST_ROW = U8 ? 256 : 512;                 // bytes of one stream's K-block in the staging ring
+    constexpr int ST_BYTES = 32 * ST_ROW;
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bar_full[MAX_RING], bar_empty[MAX_RING], bar_acc_full[2], bar_acc_empty[2];
     __shared__ __align__(8) uint64_t bar_st_full[MAX_STAGE], bar_st_empty[MAX_STAGE];
@@ -205,8 +237,10 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                 for (long m = pc.j0; m < m_end; m++) {
                     if (!staged(m)) continue;
                     mbar_wait(&bar_st_empty[q_slot], q_par ^ 1);                 // every producer has read the slot
-                    mbar_expect_tx(&bar_st_full[q_slot], TILE_BYTES);
-                    tma_rows(smem_u32(stage) + (uint32_t)q_slot * TILE_BYTES, &map_cur, (int)(X0 + 128 * m), pc.g * 32, &bar_st_full[q_slot]);
+                    mbar_expect_tx(&bar_st_full[q_slot], ST_BYTES);
+                    // (the map's elements are 32-bit words: one int16 sample, or two u8 samples)
+                    tma_rows(smem_u32(stage) + (uint32_t)q_slot * TILE_BYTES, &map_cur, (int)((X0 + 128 * m) >> (U8 ? 1 : 0)), pc.g * 32,
+                             &bar_st_full[q_slot]);
                     if (++q_slot == Q) { q_slot = 0; q_par ^= 1; }
                 }
             }
@@ -220,7 +254,7 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
         uint32_t soff[4];                                  // swizzled byte offsets of this thread's four plane rows (q = 0)
 #pragma unroll
         for (int k = 0; k < 4; k++) soff[k] = swz(4 * pw + k, 4 * lane);
-        const uint32_t st_off = (uint32_t)pw * 512u + (uint32_t)lane * 16u;   // this lane's 4 samples of staged row pw (+ N_PROD_WARPS q rows)
+        const uint32_t st_off = (uint32_t)pw * ST_ROW + (uint32_t)lane * (U8 ? 8u : 16u);   // this lane's 4 samples of staged row pw (+ N_PROD_WARPS q rows)
         PieceIter it(p);
         Piece pc;
         while (it.next(pc)) {
@@ -232,9 +266,15 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                     mbar_wait(&bar_st_full[q_slot], q_par);
                     const uint32_t sa = stage_sa + (uint32_t)q_slot * TILE_BYTES + st_off;
 #pragma unroll
-                    for (int q = 0; q < RPW; q++)
-                        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                                     : "=r"(v[q].x), "=r"(v[q].y), "=r"(v[q].z), "=r"(v[q].w) : "r"(sa + q * ROW_STEP));
+                    for (int q = 0; q < RPW; q++) {
+                        if (U8) {
+                            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v[q].x), "=r"(v[q].y) : "r"(sa + q * (N_PROD_WARPS * ST_ROW)));
+                            v[q].z = v[q].w = 0u;
+                        } else {
+                            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                         : "=r"(v[q].x), "=r"(v[q].y), "=r"(v[q].z), "=r"(v[q].w) : "r"(sa + q * ROW_STEP));
+                        }
+                    }
                     // release the slot BEFORE waiting for room in the operand ring, so that the TMA runs ahead of the MMA
                     // instead of in step with it (the arrive has release semantics: this thread's loads above are ordered
                     // before it, and the issuer puts a proxy fence between its acquire and the refill)
@@ -247,10 +287,12 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
 #pragma unroll
                     for (int q = 0; q < RPW; q++) {
                         const int s = s_base + pw + N_PROD_WARPS * q;
-                        v[q].x = load_i16(p, s, n0);
-                        v[q].y = load_i16(p, s, n0 + 1);
-                        v[q].z = load_i16(p, s, n0 + 2);
-                        v[q].w = load_i16(p, s, n0 + 3);
+                        // (u8 rows: the four samples as int16 pair words -- this path only serves the K-blocks that reach
+                        // into the history and rows TMA cannot address, so the int16 split below is reused as it is)
+                        v[q].x = U8 ? load_u8_as_i16(p, s, n0) : load_i16(p, s, n0);
+                        v[q].y = U8 ? load_u8_as_i16(p, s, n0 + 1) : load_i16(p, s, n0 + 1);
+                        v[q].z = U8 ? load_u8_as_i16(p, s, n0 + 2) : load_i16(p, s, n0 + 2);
+                        v[q].w = U8 ? load_u8_as_i16(p, s, n0 + 3) : load_i16(p, s, n0 + 3);
                     }
                 }
                 const int slot = p_slot;                   // ring position and lap parity advance without divisions
@@ -260,10 +302,20 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                 const uint32_t tile = ring_sa + (uint32_t)slot * TILE_BYTES;
 #pragma unroll
                 for (int q = 0; q < RPW; q++) {
-                    const uint32_t t01 = __byte_perm(v[q].x, v[q].y, 0x5140), t23 = __byte_perm(v[q].z, v[q].w, 0x5140);
-                    const uint32_t u01 = __byte_perm(v[q].x, v[q].y, 0x7362), u23 = __byte_perm(v[q].z, v[q].w, 0x7362);
-                    const uint32_t il = __byte_perm(t01, t23, 0x5410), ih = __byte_perm(t01, t23, 0x7632) ^ 0x80808080u;
-                    const uint32_t ql = __byte_perm(u01, u23, 0x5410), qh = __byte_perm(u01, u23, 0x7632) ^ 0x80808080u;
+                    uint32_t il, ih, ql, qh;
+                    if (U8 && staged(m)) {
+                        // x = (I0 Q0 I1 Q1), y = (I2 Q2 I3 Q3) offset binary: lo plane b ^ 0x80, biased hi plane 0x80 for
+                        // b >= 128 and 0x7F below (sign-replicating PRMT: 0xFF where the byte's top bit is set)
+                        il = prmt(v[q].x, v[q].y, 0x6420) ^ 0x80808080u;
+                        ql = prmt(v[q].x, v[q].y, 0x7531) ^ 0x80808080u;
+                        ih = prmt(v[q].x, v[q].y, 0xECA8) ^ 0x7F7F7F7Fu;      // selector bit 3: the byte's sign, replicated
+                        qh = prmt(v[q].x, v[q].y, 0xFDB9) ^ 0x7F7F7F7Fu;
+                    } else {
+                        const uint32_t t01 = __byte_perm(v[q].x, v[q].y, 0x5140), t23 = __byte_perm(v[q].z, v[q].w, 0x5140);
+                        const uint32_t u01 = __byte_perm(v[q].x, v[q].y, 0x7362), u23 = __byte_perm(v[q].z, v[q].w, 0x7362);
+                        il = __byte_perm(t01, t23, 0x5410), ih = __byte_perm(t01, t23, 0x7632) ^ 0x80808080u;
+                        ql = __byte_perm(u01, u23, 0x5410), qh = __byte_perm(u01, u23, 0x7632) ^ 0x80808080u;
+                    }
                     // rows 4*(pw + N_PROD_WARPS*q) + k: the swizzle term (row & 7) does not depend on q, and tile rows
                     // 4*N_PROD_WARPS apart are ROW_STEP bytes apart
                     asm volatile("st.shared.b32 [%0], %1;" ::"r"(tile + soff[0] + q * ROW_STEP), "r"(il) : "memory");
@@ -406,7 +458,8 @@ static int launch_toeplitz_rows(const ToepParams &p_in, cudaStream_t st)
     if (p.n_out <= 0 || p.n_streams <= 0) return SFE_OK;
     p.n_groups = (p.n_streams + 31) / 32;
     p.n_steps = (p.n_out + TNO - 1) / TNO;
-    if (p.KB < 1 || p.KB + 2 > MAX_RING || p.in.fmt != SFE_IN_I16) {
+    const bool u8 = p.in.fmt == SFE_IN_U8;
+    if (p.KB < 1 || p.KB + 2 > MAX_RING || (p.in.fmt != SFE_IN_I16 && !u8)) {
         set_error("toeplitz_i8: unsupported configuration");
         return SFE_ERR_ARG;
     }
@@ -417,9 +470,15 @@ static int launch_toeplitz_rows(const ToepParams &p_in, cudaStream_t st)
     static const bool no_tma = getenv("SFE_TOEP_NO_TMA") != nullptr;       // tuning hook: producers load from global memory
     // (a box must start on a 16-byte boundary of its row: calls whose first output does not sit on a multiple of four samples
     // -- a stream fed in pieces that are not multiples of 8 samples -- keep the producers' own loads)
-    p.use_tma = !no_tma && (reinterpret_cast<uintptr_t>(p.in.cur) & 15) == 0 && (p.in.pitch & 3) == 0 && p.in.n >= 128 &&
-                ((p.n_first - 128L * (p.KB - 1)) & 3) == 0;
-    if (p.use_tma && !sfe_plain_map_2d(&map, p.in.cur, p.in.n, p.n_streams, p.in.pitch, 128, 32)) return SFE_ERR_CUDA;
+    const int amask = u8 ? 7 : 3;            // samples per 16 bytes, minus one
+    p.use_tma = !no_tma && (reinterpret_cast<uintptr_t>(p.in.cur) & 15) == 0 && (p.in.pitch & amask) == 0 && p.in.n >= 128 &&
+                ((p.n_first - 128L * (p.KB - 1)) & amask) == 0;
+    // the map's elements are 32-bit words: one int16 sample or two u8 samples.  An odd u8 row length lets the last word carry
+    // one byte pair from behind the row's end (inside its pitch): it sits at sample index n, which only meets zero taps
+    // of the outputs a call produces
+    if (p.use_tma && !sfe_plain_map_2d(&map, p.in.cur, u8 ? (p.in.n + 1) / 2 : p.in.n, p.n_streams, u8 ? p.in.pitch / 2 : p.in.pitch,
+                                       u8 ? 64 : 128, 32))
+        return SFE_ERR_CUDA;
     static const int stage_env = getenv("SFE_TOEP_STAGE") ? atoi(getenv("SFE_TOEP_STAGE")) : 0;   // tuning hook: staging depth
     const size_t b_bytes = ((size_t)(p.KB * TNCOL * 128 + 1023) & ~(size_t)1023);
     auto smem_for = [&](int ring, int stage) { return b_bytes + (size_t)(ring + stage) * TILE_BYTES + 1024; };
@@ -438,7 +497,8 @@ static int launch_toeplitz_rows(const ToepParams &p_in, cudaStream_t st)
         set_error("toeplitz_i8: tap count too large for shared memory");
         return SFE_ERR_ARG;
     }
-    if (!SFE_CUDA(cudaFuncSetAttribute(toeplitz_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
+    void (*kern)(const CUtensorMap, const ToepParams) = u8 ? toeplitz_i8_kernel<SFE_IN_U8> : toeplitz_i8_kernel<SFE_IN_I16>;
+    if (!SFE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))) return SFE_ERR_CUDA;
     int dev = 0, sms = 0;
     if (!SFE_CUDA(cudaGetDevice(&dev)) || !SFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev))) return SFE_ERR_CUDA;
     const long F = (long)p.n_groups * p.n_steps;
@@ -448,7 +508,7 @@ static int launch_toeplitz_rows(const ToepParams &p_in, cudaStream_t st)
     static const bool one_cta = getenv("SFE_TOEP_ONE_CTA") != nullptr;   // tuning hook
     const int per_sm = (2 * (smem + 2048) <= 227 * 1024 && !one_cta) ? 2 : 1;
     if (grid > (long)sms * per_sm) grid = (long)sms * per_sm;
-    toeplitz_i8_kernel<<<(unsigned)grid, N_THREADS, smem, st>>>(map, p);
+    kern<<<(unsigned)grid, N_THREADS, smem, st>>>(map, p);
     count_launch();
     return SFE_CUDA(cudaGetLastError()) ? SFE_OK : SFE_ERR_CUDA;
 }
@@ -507,7 +567,7 @@ int launch_toeplitz(const ToepParams &p, cudaStream_t st)
 
 // Host side: quantise g to 24-bit fixed point, split into three signed base-256 digits and lay the banded
 // Toeplitz blocks out exactly as the kernel's shared-memory image (K-major, SWIZZLE_128B).
-bool toeplitz_prepare(const std::vector<double> &g, ToepHost &h)
+bool toeplitz_prepare(const std::vector<double> &g, ToepHost &h, int in_fmt)
 {
     const int T = (int)g.size();
     h.KB = (T - 1 + 127) / 128 + 1;
@@ -531,7 +591,8 @@ bool toeplitz_prepare(const std::vector<double> &g, ToepHost &h)
         sum[1] += d1[j];
         sum[2] += d2[j];
     }
-    const double Kq = sigma / Zmax / 32767.0;             // x = s/32767, folded into the weights
+    // x = s/32767 or (b - 128)/127 (source_c_impl.cc:121-132), folded into the weights
+    const double Kq = sigma / Zmax / (in_fmt == SFE_IN_U8 ? 127.0 : 32767.0);
     h.w[0] = (float)(Kq * 65536.0);
     h.w[1] = (float)(Kq * 256.0);
     h.w[2] = (float)Kq;

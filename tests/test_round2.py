@@ -391,3 +391,50 @@ def test_bank_seam_exchange_random_shapes(gpu_lib, oracle_lib, seed):
         for k, s in enumerate(rows):
             nrms, peak = F.err_metrics(runs[0][s], ref[k])
             assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (base, fmt, S, N, cut, s, nrms, peak)
+
+
+# ---- the tensor-core decimator on the u8 wire format (one signed byte plane per component) ---------------------------------
+
+@pytest.mark.parametrize("base,S,N", [("cfg2_small", 33, 50003), ("cfg5_small", 40, 70001), ("cfg2_small", 8, 4099)])
+def test_tensor_path_u8_vs_oracle(gpu_lib, oracle_lib, base, S, N):
+    """u8 rows (source_c_impl.cc:121-132: (b - 128) / 127) through toeplitz_i8_kernel<u8>: against the reference classes, and
+    against the CUDA-core plan of the same chain; every byte value occurs, with runs of the corners 0 / 255 / 128"""
+    from oracle import oracle as O
+    cfg = dict(F.CONFIGS[base], in_fmt=F.IN_U8, S=S, N=N)
+    iq = F.make_input(cfg)
+    iq[0, :300] = 255
+    iq[1, :300] = 0
+    iq[2, 100:400, 0] = 128
+    iq[3, :256, 0] = np.arange(256, dtype=np.uint8)
+    iq[3, :256, 1] = np.arange(256, dtype=np.uint8)[::-1]
+    ref, _ = O.chain_run(iq, F.IN_U8, cfg.get("blkconv"), cfg.get("stage_a"), cfg.get("stage_b"), lib=oracle_lib, n_threads=4)
+    ch = _chain(cfg, flags=8)             # 8: no fused bank, so that the decimator runs as a kernel of its own
+    assert "toeplitz_i8_tcgen05" in ch.plan, ch.plan
+    got = ch.process(iq)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    nrms, peak = F.err_metrics(got, ref)
+    assert nrms <= F.NRMS_TOL and peak <= F.PEAK_TOL, (ch.plan, nrms, peak)
+    alt_ch = _chain(cfg, flags=8 + 4)     # 4: no tensor cores
+    assert "toeplitz" not in alt_ch.plan
+    nrms, peak = F.err_metrics(got, alt_ch.process(iq))
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
+
+
+def test_tensor_path_u8_ragged_calls(gpu_lib):
+    """a u8 stream fed in ragged pieces (TMA-staged and self-loaded K-blocks mixed, odd row lengths): same samples as one call"""
+    cfg = dict(F.CONFIGS["cfg2_small"], in_fmt=F.IN_U8, S=9, N=40000)
+    iq = F.make_input(cfg)
+    one = _chain(cfg).process(iq)
+    ch = _chain(cfg)
+    assert "toeplitz_i8_tcgen05" in ch.plan, ch.plan
+    parts, off = [], 0
+    for n in (1, 7, 1000, 4096, 12345, 3, 8192, 10 ** 9):
+        n = min(n, cfg["N"] - off)
+        if n <= 0:
+            break
+        parts.append(ch.process(iq[:, off:off + n]))
+        off += n
+    got = np.concatenate(parts, axis=1)
+    assert got.shape == one.shape
+    nrms, peak = F.err_metrics(got, one)
+    assert nrms <= 2e-6 and peak <= 1e-5, (nrms, peak)
