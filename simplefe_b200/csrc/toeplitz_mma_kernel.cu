@@ -46,6 +46,9 @@ namespace sfe {
 
 namespace {
 
+#ifndef SFE_TOEP_QUAD_STORE
+#define SFE_TOEP_QUAD_STORE 1
+#endif
 #ifndef SFE_TOEP_EARLY_RELEASE
 #define SFE_TOEP_EARLY_RELEASE 0
 #endif
@@ -404,6 +407,8 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
         // the bias of the hi planes (128 * sum of the digit's taps, an exact integer) is removed in int32, before conversion
         const int ci0 = hi ? (int)p.corr[0] : 0, ci1 = hi ? (int)p.corr[1] : 0, ci2 = hi ? (int)p.corr[2] : 0;
         long step = 0;
+        // 128-bit stores need 16-byte aligned output rows
+        const bool out_vec = (reinterpret_cast<uintptr_t>(p.out) & 15) == 0 && (p.out_pitch & 1) == 0;
         PieceIter it(p);
         Piece pc;
         while (it.next(pc)) {
@@ -430,6 +435,42 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                 }
                 asm volatile("tcgen05.fence::before_thread_sync;");
                 mbar_arrive(&bar_acc_empty[a]);            // TMEM buffer free for the step after next
+#if SFE_TOEP_QUAD_STORE
+                // The four lanes of a stream hold the partial sums (I_lo, I_hi, Q_lo, Q_hi) of all 16 outputs.  Two exchange
+                // rounds in halves leave every lane with BOTH components of four consecutive outputs: round 1 with the lane
+                // of the other byte (lo + 256 hi; the even lane keeps outputs 0-7, the odd one 8-15), round 2 with the lane
+                // of the other component (the I lane keeps the first four of its eight, the Q lane the last four).  12
+                // shuffles per lane instead of 32, and each lane stores its 32 bytes as two 128-bit words: every sector of
+                // the output row is written once, by one instruction (with one lane of four storing 16 float2 one by one,
+                // every sector was written four times -- removing the stores alone made the kernel 15 % faster).
+                float g8[8];
+#pragma unroll
+                for (int t = 0; t < 8; t++) {
+                    const float send = (plane & 1) ? f[t] : f[t + 8];
+                    const float keep = (plane & 1) ? f[t + 8] : f[t];
+                    g8[t] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+                }
+                float2 o4[4];
+#pragma unroll
+                for (int t = 0; t < 4; t++) {
+                    const float send = (plane & 2) ? g8[t] : g8[t + 4];
+                    const float recv = __shfl_xor_sync(0xffffffffu, send, 2);
+                    o4[t] = (plane & 2) ? make_float2(recv, g8[t + 4]) : make_float2(g8[t], recv);
+                }
+                const int k_off = 8 * (plane & 1) + 4 * (plane >> 1);     // first of this lane's four outputs within the step
+                const long k_abs = j * TNO + k_off;
+                float2 *o = p.out + (long)s * p.out_pitch + k_abs;
+                if (s < p.n_streams) {
+                    if (k_abs + 4 <= p.n_out && out_vec) {
+                        reinterpret_cast<float4 *>(o)[0] = make_float4(o4[0].x, o4[0].y, o4[1].x, o4[1].y);
+                        reinterpret_cast<float4 *>(o)[1] = make_float4(o4[2].x, o4[2].y, o4[3].x, o4[3].y);
+                    } else {
+#pragma unroll
+                        for (int t = 0; t < 4; t++)
+                            if (k_abs + t < p.n_out) o[t] = o4[t];
+                    }
+                }
+#else
                 float2 *o = p.out + (long)s * p.out_pitch + j * TNO;
 #pragma unroll
                 for (int i = 0; i < TNO; i++) {
@@ -438,6 +479,7 @@ __global__ void __launch_bounds__(N_THREADS, 2) toeplitz_i8_kernel(const __grid_
                     const float q = __shfl_down_sync(0xffffffffu, fi, 2); // Q next to I
                     if (plane == 0 && s < p.n_streams && j * TNO + i < p.n_out) o[i] = make_float2(fi, q);
                 }
+#endif
             }
         }
     }
