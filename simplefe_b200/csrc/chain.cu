@@ -407,7 +407,10 @@ int run_ops(sfe_chain *c, Workspace &w, int s0, int ns, const void *d_in, long i
             rc = launch_decim_fir(p, st);
         } else if (op.kind == OP_TOEP && op.n_out > 0) {
             // the kernel stages the rows by TMA, which needs 16-byte aligned rows: realign caller buffers that are not
-            if (((reinterpret_cast<uintptr_t>(src) & 15) || ((src_pitch * eb) & 15)) && op.n_in >= 128) {
+            // (u8 rows of odd length too: the tensor map's elements are two samples wide, so its last word reaches one sample
+            // past the row's end -- harmless inside a buffer of our own, not something to read from the caller's last row)
+            if (((reinterpret_cast<uintptr_t>(src) & 15) || ((src_pitch * eb) & 15) || (op.in_fmt == SFE_IN_U8 && (op.n_in & 1))) &&
+                op.n_in >= 128) {
                 const long ap = (op.n_in + 7) & ~7L;
                 if (!ensure(&w.d_align, &w.align_bytes, (size_t)ns * ap * eb)) return SFE_ERR_CUDA;
                 if (!SFE_CUDA(cudaMemcpy2DAsync(w.d_align, (size_t)ap * eb, src, (size_t)src_pitch * eb, (size_t)op.n_in * eb, ns,

@@ -517,7 +517,8 @@ static int launch_toeplitz_rows(const ToepParams &p_in, cudaStream_t st)
                 ((p.n_first - 128L * (p.KB - 1)) & amask) == 0;
     // the map's elements are 32-bit words: one int16 sample or two u8 samples.  An odd u8 row length lets the last word carry
     // one byte pair from behind the row's end (inside its pitch): it sits at sample index n, which only meets zero taps
-    // of the outputs a call produces
+    // of the outputs a call produces (chain.cu hands such rows over in a staging buffer of its own, so the read never
+    // leaves memory the library owns)
     if (p.use_tma && !sfe_plain_map_2d(&map, p.in.cur, u8 ? (p.in.n + 1) / 2 : p.in.n, p.n_streams, u8 ? p.in.pitch / 2 : p.in.pitch,
                                        u8 ? 64 : 128, 32))
         return SFE_ERR_CUDA;
